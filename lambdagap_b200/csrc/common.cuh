@@ -1,0 +1,186 @@
+// common.cuh -- shared device/host declarations of the B200-native tree learner (sm_100a only).
+//
+// Layout conventions:
+//   * bins are *mapper* bins (what BinIterator::Get returns in the reference), one byte per cell;
+//   * canonical storage is column-major  col_bins[F][col_stride]  (partition, streaming histogram);
+//   * a row-major mirror  row_bins[N][row_stride]  (row_stride = 32 * num_tiles) serves gathers: one 32-byte
+//     sector per (row, 32-feature tile);
+//   * histograms live in HBM as  hist[slot][tile][256 bins][32 lanes]  of exact integers:
+//       float mode     : {int64 grad_fix, int64 hess_fix} fixed-point (power-of-two scale per tree)
+//       quantized mode : int64 = (int32 grad_sum << 32) | uint32 hess_sum   (the reference's 32-bit packing,
+//                        src/treelearner/feature_histogram.hpp:215-216)
+#pragma once
+#include <cuda_runtime.h>
+
+#include <atomic>
+#include <cstdarg>
+#include <cstdint>
+#include <cstdio>
+#include <stdexcept>
+#include <string>
+
+#include "lambdagap_b200.h"
+
+namespace gbl {
+
+constexpr int kMaxBin = 256;       // bins per feature held by one histogram row block
+constexpr int kTile = 32;          // features per tile = lanes per warp
+constexpr int kTailWords = 8;      // int64 words appended to every histogram slot (data-parallel counts)
+constexpr int kNumSM = 148;        // B200
+
+// include/LightGBM/meta.h:54-56: const double kEpsilon = 1e-15f; kMinScore = -inf
+#define GBL_KEPS (static_cast<double>(1e-15f))
+
+struct GblError : public std::runtime_error {
+  explicit GblError(const std::string& m) : std::runtime_error(m) {}
+};
+
+void set_last_error(const char* msg);
+[[noreturn]] void fatal(const char* fmt, ...);
+extern std::atomic<long long> g_kernel_launches;
+
+#define GBL_CUDA(call)                                                                              \
+  do {                                                                                              \
+    cudaError_t e__ = (call);                                                                       \
+    if (e__ != cudaSuccess) ::gbl::fatal("CUDA error %s at %s:%d: %s", cudaGetErrorName(e__), __FILE__, \
+                                          __LINE__, cudaGetErrorString(e__));                      \
+  } while (0)
+
+#define GBL_LAUNCH(kernel, grid, block, smem, stream, ...)                   \
+  do {                                                                       \
+    kernel<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__);              \
+    ::gbl::g_kernel_launches.fetch_add(1, std::memory_order_relaxed);        \
+    GBL_CUDA(cudaGetLastError());                                            \
+  } while (0)
+
+#define GBL_API_BEGIN() try {
+#define GBL_API_END()                                   \
+  }                                                     \
+  catch (const std::exception& ex) {                    \
+    ::gbl::set_last_error(ex.what());                   \
+    return -1;                                          \
+  }                                                     \
+  catch (...) {                                         \
+    ::gbl::set_last_error("unknown exception");        \
+    return -1;                                          \
+  }                                                     \
+  return 0;
+
+inline int64_t round_up(int64_t x, int64_t m) { return (x + m - 1) / m * m; }
+
+// ------------------------------------------------------------------------------------------------ device structs
+struct FeatMeta {
+  int num_bin;
+  int missing_type;
+  int default_bin;
+  int most_freq_bin;
+  int real_index;
+  int offset;  // most_freq_bin == 0 (FeatureMetainfo::offset, feature_histogram.hpp:1429-1433)
+  double penalty;
+};
+
+// SplitInfo (src/treelearner/split_info.hpp:22-54) restricted to numerical splits
+struct BestSplit {
+  double gain;
+  int feature;       // inner index, -1 = none
+  int real_feature;  // original column, -1 = none
+  unsigned threshold;
+  int default_left;
+  int left_count;
+  int right_count;
+  double left_output;
+  double right_output;
+  double left_sum_g;
+  double left_sum_h;
+  double right_sum_g;
+  double right_sum_h;
+  long long left_ig;  // exact integer sums (float mode: fixed point; quantized: int grad / hess sums)
+  long long left_ih;
+  long long right_ig;
+  long long right_ih;
+};
+
+// LeafSplits (src/treelearner/leaf_splits.hpp:22-275) + DataPartition bookkeeping + best_split_per_leaf_
+struct LeafState {
+  int begin;
+  int count;         // local rows
+  int global_count;  // rows over all ranks
+  int depth;
+  int buf;           // which index buffer holds the segment
+  int slot;          // histogram slot
+  int pad0;
+  int pad1;
+  double sum_g;
+  double sum_h;
+  long long ig;
+  long long ih;
+  double output;  // LeafSplits::weight(), parent_output of the children
+  BestSplit best;
+};
+
+struct TreeState {
+  int num_leaves_cur;
+  int done;          // no further split with positive gain
+  int num_splits;
+  int smaller;       // leaves of the upcoming FindBestSplits round (-1 = none)
+  int larger;
+  int skip_hist;     // BeforeFindBestSplit said no (single GPU shortcut)
+  int do_split;      // select produced a split for this round
+  int split_leaf;
+  int split_feature;
+  unsigned split_threshold;
+  int split_default_left;
+  int split_left_total;  // filled by the partition
+  unsigned scan_done_counter;
+  unsigned part_done_counter;
+  unsigned part_ticket;
+  int pad;
+  // float mode fixed-point scales (powers of two): value_fix = value * g_scale ; value = fix * g_inv
+  double g_scale, g_inv, h_scale, h_inv;
+  // quantized mode (GradientDiscretizer): grad_scale/hess_scale and inverses
+  double q_grad_scale, q_hess_scale, q_inv_grad_scale, q_inv_hess_scale;
+  float max_abs_g, max_abs_h;
+  double root_output;
+};
+
+struct LearnerParams {  // by-value kernel argument
+  int num_leaves;
+  int max_depth;
+  int min_data_in_leaf;
+  int quantized;
+  int num_grad_quant_bins;
+  int is_constant_hessian;
+  int num_features;
+  int num_tiles;
+  int num_ranks;
+  int pad;
+  double min_sum_hessian_in_leaf;
+  double lambda_l1, lambda_l2, min_gain_to_split, max_delta_step, path_smooth;
+};
+
+// ------------------------------------------------------------------------------------------------ host objects
+struct Dataset {
+  int device = 0;
+  int64_t num_data = 0;
+  int num_features = 0;
+  int num_tiles = 0;
+  int64_t col_stride = 0;  // bytes between feature columns
+  int row_stride = 0;      // bytes between rows of the mirror
+  uint8_t* col_bins = nullptr;
+  uint8_t* row_bins = nullptr;
+  FeatMeta* meta_dev = nullptr;
+  FeatMeta* meta_host = nullptr;
+};
+
+struct DeviceGuard {
+  int prev = -1;
+  explicit DeviceGuard(int dev) {
+    GBL_CUDA(cudaGetDevice(&prev));
+    if (prev != dev) GBL_CUDA(cudaSetDevice(dev));
+  }
+  ~DeviceGuard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+
+}  // namespace gbl

@@ -1,0 +1,615 @@
+// learner.cu -- host side of the device tree learner + its C ABI.
+//
+// Mirrors SerialTreeLearner::Train (src/treelearner/serial_tree_learner.cpp:179-245) and, with a communicator,
+// DataParallelTreeLearner (src/treelearner/data_parallel_tree_learner.cpp:123-463).  The whole leaf-wise loop
+// (up to num_leaves-1 dependent rounds of histogram -> scan/arg-max -> partition) is enqueued on one stream with
+// fixed launch shapes; every kernel reads the leaf it works on from device memory, so the host never waits
+// inside a tree (the reference CUDA learner synchronises twice per split,
+// src/treelearner/cuda/cuda_single_gpu_tree_learner.cpp:246-325).  With GBL_USE_GRAPH=1 (default) the round
+// sequence is captured once into a CUDA graph and replayed per tree.
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+#include "comm.cuh"
+#include "kernels.cuh"
+
+namespace gbl {
+
+struct Learner {
+  const Dataset* ds = nullptr;
+  gbl_learner_config cfg{};
+  Comm* comm = nullptr;
+  cudaStream_t stream = nullptr;
+  LearnerDev dev{};
+  // owned device memory
+  TreeState* ts = nullptr;
+  LeafState* leaves = nullptr;
+  int* idx[2] = {nullptr, nullptr};
+  int2* gh_fix = nullptr;
+  short* gh_q = nullptr;
+  long long* hist_pool = nullptr;
+  size_t hist_pool_words = 0;
+  unsigned char* splittable = nullptr;
+  signed char* feature_mask = nullptr;
+  BestSplit* cand = nullptr;
+  gbl_split_record* records = nullptr;
+  int* block_counts = nullptr;
+  double* leaf_values = nullptr;
+  double* leaf_values_tmp = nullptr;
+  double* rand_g = nullptr;
+  double* rand_h = nullptr;
+  int64_t rand_n = 0;
+  int rand_start = 0;
+  int* bag_indices = nullptr;
+  int bag_count = 0;
+  float* grad_stage = nullptr;  // train_host staging
+  float* hess_stage = nullptr;
+  long long* tap_hist = nullptr;
+  // pinned host mirrors
+  gbl_split_record* records_pinned = nullptr;
+  TreeState* ts_pinned = nullptr;
+  // graph
+  bool use_graph = true;
+  cudaGraphExec_t graph_exec = nullptr;
+  const float* graph_grad = nullptr;
+  const float* graph_hess = nullptr;
+  int graph_rand_start = -1;
+  const int* graph_bag = nullptr;
+  int graph_bag_count = -1;
+  bool tree_pending = false;
+  bool has_tree = false;
+};
+
+static void validate_config(const gbl_learner_config& c) {
+  if (c.num_leaves < 2) fatal("learner: num_leaves must be >= 2 (got %d)", c.num_leaves);
+  if (c.num_leaves > 32768) fatal("learner: num_leaves=%d too large", c.num_leaves);
+  if (c.min_data_in_leaf < 0) fatal("learner: min_data_in_leaf must be >= 0");
+  if (c.use_quantized_grad && (c.num_grad_quant_bins < 2 || c.num_grad_quant_bins > 126))
+    fatal("learner: num_grad_quant_bins=%d unsupported (2..126)", c.num_grad_quant_bins);
+  if (c.lambda_l1 < 0 || c.lambda_l2 < 0) fatal("learner: lambda_l1 / lambda_l2 must be >= 0");
+}
+
+static LearnerParams make_params(const Learner* L) {
+  LearnerParams p{};
+  const gbl_learner_config& c = L->cfg;
+  p.num_leaves = c.num_leaves;
+  p.max_depth = c.max_depth;
+  p.min_data_in_leaf = c.min_data_in_leaf;
+  p.quantized = c.use_quantized_grad ? 1 : 0;
+  p.num_grad_quant_bins = c.num_grad_quant_bins;
+  p.is_constant_hessian = c.is_constant_hessian ? 1 : 0;
+  p.num_features = L->ds->num_features;
+  p.num_tiles = L->ds->num_tiles;
+  p.num_ranks = L->comm != nullptr ? L->comm->num_ranks : 1;
+  p.min_sum_hessian_in_leaf = c.min_sum_hessian_in_leaf;
+  p.lambda_l1 = c.lambda_l1;
+  p.lambda_l2 = c.lambda_l2;
+  p.min_gain_to_split = c.min_gain_to_split;
+  p.max_delta_step = c.max_delta_step;
+  p.path_smooth = c.path_smooth;
+  return p;
+}
+
+static void drop_graph(Learner* L) {
+  if (L->graph_exec != nullptr) {
+    cudaGraphExecDestroy(L->graph_exec);
+    L->graph_exec = nullptr;
+  }
+}
+
+static void free_tree_buffers(Learner* L) {
+  cudaFree(L->leaves);
+  cudaFree(L->hist_pool);
+  cudaFree(L->splittable);
+  cudaFree(L->records);
+  cudaFree(L->leaf_values);
+  cudaFree(L->leaf_values_tmp);
+  if (L->records_pinned) cudaFreeHost(L->records_pinned);
+  L->leaves = nullptr;
+  L->hist_pool = nullptr;
+  L->splittable = nullptr;
+  L->records = nullptr;
+  L->leaf_values = nullptr;
+  L->leaf_values_tmp = nullptr;
+  L->records_pinned = nullptr;
+}
+
+// (re)allocates everything that depends on the config
+static void alloc_tree_buffers(Learner* L) {
+  const Dataset* ds = L->ds;
+  const int nl = L->cfg.num_leaves;
+  const long long entry_words = L->cfg.use_quantized_grad ? 1 : 2;
+  const long long slot_stride = static_cast<long long>(ds->num_tiles) * kMaxBin * kTile * entry_words + kTailWords;
+  L->hist_pool_words = static_cast<size_t>(slot_stride) * nl;
+  GBL_CUDA(cudaMalloc(&L->leaves, sizeof(LeafState) * nl));
+  GBL_CUDA(cudaMalloc(&L->hist_pool, sizeof(long long) * L->hist_pool_words));
+  GBL_CUDA(cudaMalloc(&L->splittable, static_cast<size_t>(nl) * ds->num_features));
+  GBL_CUDA(cudaMalloc(&L->records, sizeof(gbl_split_record) * nl));
+  GBL_CUDA(cudaMemset(L->records, 0, sizeof(gbl_split_record) * nl));
+  GBL_CUDA(cudaMalloc(&L->leaf_values, sizeof(double) * nl));
+  GBL_CUDA(cudaMalloc(&L->leaf_values_tmp, sizeof(double) * nl));
+  GBL_CUDA(cudaMallocHost(&L->records_pinned, sizeof(gbl_split_record) * nl));
+  LearnerDev& d = L->dev;
+  d.leaves = L->leaves;
+  d.hist_pool = L->hist_pool;
+  d.slot_stride = slot_stride;
+  d.splittable = L->splittable;
+  d.records = L->records;
+  d.leaf_values = L->leaf_values;
+  d.p = make_params(L);
+}
+
+static Learner* learner_create(const Dataset* ds, const gbl_learner_config* cfg, Comm* comm) {
+  if (ds == nullptr || cfg == nullptr) fatal("gbl_learner_create: null argument");
+  validate_config(*cfg);
+  if (comm != nullptr && comm->device != ds->device) fatal("learner: communicator and dataset on different devices");
+  DeviceGuard guard(ds->device);
+  cudaDeviceProp prop;
+  GBL_CUDA(cudaGetDeviceProperties(&prop, ds->device));
+  if (prop.major != 10) fatal("learner: device %d is sm_%d%d; this library is built for sm_100a (B200) only", ds->device,
+                              prop.major, prop.minor);
+  Learner* L = new Learner();
+  L->ds = ds;
+  L->cfg = *cfg;
+  L->comm = comm;
+  const char* g = std::getenv("GBL_USE_GRAPH");
+  L->use_graph = !(g != nullptr && g[0] == '0');
+  GBL_CUDA(cudaStreamCreateWithFlags(&L->stream, cudaStreamNonBlocking));
+  const size_t n = static_cast<size_t>(ds->num_data);
+  GBL_CUDA(cudaMalloc(&L->ts, sizeof(TreeState)));
+  GBL_CUDA(cudaMemset(L->ts, 0, sizeof(TreeState)));
+  GBL_CUDA(cudaMalloc(&L->idx[0], sizeof(int) * (n + 32)));
+  GBL_CUDA(cudaMalloc(&L->idx[1], sizeof(int) * (n + 32)));
+  GBL_CUDA(cudaMalloc(&L->gh_fix, sizeof(int2) * n));
+  GBL_CUDA(cudaMalloc(&L->gh_q, sizeof(short) * n));
+  GBL_CUDA(cudaMalloc(&L->cand, sizeof(BestSplit) * 2 * ds->num_features));
+  GBL_CUDA(cudaMalloc(&L->block_counts, sizeof(int) * partition_grid()));
+  GBL_CUDA(cudaMallocHost(&L->ts_pinned, sizeof(TreeState)));
+  LearnerDev& d = L->dev;
+  d.col_bins = ds->col_bins;
+  d.row_bins = ds->row_bins;
+  d.col_stride = ds->col_stride;
+  d.row_stride = ds->row_stride;
+  d.num_data = static_cast<int>(ds->num_data);
+  d.meta = ds->meta_dev;
+  d.ts = L->ts;
+  d.idx[0] = L->idx[0];
+  d.idx[1] = L->idx[1];
+  d.gh_fix = L->gh_fix;
+  d.gh_q = L->gh_q;
+  d.feature_mask = nullptr;
+  d.cand = L->cand;
+  d.block_counts = L->block_counts;
+  d.rand_g = nullptr;
+  d.rand_h = nullptr;
+  d.rand_start = 0;
+  alloc_tree_buffers(L);
+  histogram_setup();
+  return L;
+}
+
+static void learner_free(Learner* L) {
+  if (L == nullptr) return;
+  DeviceGuard guard(L->ds->device);
+  cudaStreamSynchronize(L->stream);
+  drop_graph(L);
+  free_tree_buffers(L);
+  cudaFree(L->ts);
+  cudaFree(L->idx[0]);
+  cudaFree(L->idx[1]);
+  cudaFree(L->gh_fix);
+  cudaFree(L->gh_q);
+  cudaFree(L->cand);
+  cudaFree(L->block_counts);
+  cudaFree(L->feature_mask);
+  cudaFree(L->rand_g);
+  cudaFree(L->rand_h);
+  cudaFree(L->bag_indices);
+  cudaFree(L->grad_stage);
+  cudaFree(L->hess_stage);
+  cudaFree(L->tap_hist);
+  if (L->ts_pinned) cudaFreeHost(L->ts_pinned);
+  cudaStreamDestroy(L->stream);
+  delete L;
+}
+
+// Enqueues one whole tree on `s` (also the body captured into the CUDA graph).
+static void enqueue_tree(Learner* L, cudaStream_t s) {
+  const LearnerDev& d = L->dev;
+  const bool multi = L->comm != nullptr && L->comm->num_ranks > 1;
+  GBL_CUDA(cudaMemsetAsync(L->hist_pool, 0, sizeof(long long) * L->hist_pool_words, s));
+  launch_tree_begin(d, L->bag_indices, L->bag_count, s);
+  launch_maxabs(d, s);
+  if (multi) {
+    // GradientDiscretizer: Network::GlobalSyncUpByMax (gradient_discretizer.cpp:101-104); also used for the
+    // fixed-point scale in float mode so that every rank shares one scale.
+    comm_allreduce_f32(L->comm, &L->ts->max_abs_g, 2, RedOp::kMax, s);
+  }
+  launch_scales_and_convert(d, s);
+  const int rounds = L->cfg.num_leaves - 1;
+  for (int round = 0; round < rounds; ++round) {
+    launch_histogram(d, round, nullptr, -1, nullptr, s);
+    if (multi) {
+      // histogram + (smaller, larger) row counts in one all-reduce; replaces Network::ReduceScatter of
+      // data_parallel_tree_learner.cpp:285-297 and the count sync of :457-458
+      comm_allreduce_i64(L->comm, L->hist_pool + static_cast<long long>(round) * d.slot_stride,
+                         static_cast<size_t>(d.slot_stride), RedOp::kSum, s);
+    }
+    if (round == 0) launch_root_init(d, s);
+    launch_find_best(d, round, s);
+    launch_partition(d, round, s);
+  }
+  GBL_CUDA(cudaMemcpyAsync(L->records_pinned, L->records, sizeof(gbl_split_record) * rounds, cudaMemcpyDeviceToHost, s));
+  GBL_CUDA(cudaMemcpyAsync(L->ts_pinned, L->ts, sizeof(TreeState), cudaMemcpyDeviceToHost, s));
+}
+
+static void train_async(Learner* L, const float* grad_dev, const float* hess_dev) {
+  if (grad_dev == nullptr || hess_dev == nullptr) fatal("gbl_learner_train: null gradients");
+  if (L->cfg.use_quantized_grad && L->cfg.stochastic_rounding && L->rand_g == nullptr)
+    fatal("learner: stochastic_rounding=1 needs gbl_learner_set_quant_random (host mt19937 arrays of the reference), "
+          "or set stochastic_rounding=0");
+  DeviceGuard guard(L->ds->device);
+  LearnerDev& d = L->dev;
+  d.grad = grad_dev;
+  d.hess = hess_dev;
+  d.feature_mask = L->feature_mask;
+  d.rand_g = (L->cfg.use_quantized_grad && L->cfg.stochastic_rounding) ? L->rand_g : nullptr;
+  d.rand_h = d.rand_g != nullptr ? L->rand_h : nullptr;
+  d.rand_start = L->rand_start;
+  const bool multi = L->comm != nullptr && L->comm->num_ranks > 1;
+  if (L->use_graph && !multi) {
+    const bool stale = L->graph_exec == nullptr || L->graph_grad != grad_dev || L->graph_hess != hess_dev ||
+                       L->graph_rand_start != d.rand_start || L->graph_bag != L->bag_indices ||
+                       L->graph_bag_count != L->bag_count;
+    if (stale) {
+      drop_graph(L);
+      cudaGraph_t graph = nullptr;
+      GBL_CUDA(cudaStreamBeginCapture(L->stream, cudaStreamCaptureModeThreadLocal));
+      try {
+        enqueue_tree(L, L->stream);
+      } catch (...) {
+        cudaStreamEndCapture(L->stream, &graph);
+        if (graph) cudaGraphDestroy(graph);
+        throw;
+      }
+      GBL_CUDA(cudaStreamEndCapture(L->stream, &graph));
+      GBL_CUDA(cudaGraphInstantiate(&L->graph_exec, graph, 0));
+      cudaGraphDestroy(graph);
+      L->graph_grad = grad_dev;
+      L->graph_hess = hess_dev;
+      L->graph_rand_start = d.rand_start;
+      L->graph_bag = L->bag_indices;
+      L->graph_bag_count = L->bag_count;
+    }
+    GBL_CUDA(cudaGraphLaunch(L->graph_exec, L->stream));
+  } else {
+    enqueue_tree(L, L->stream);
+  }
+  L->tree_pending = true;
+  L->has_tree = true;
+}
+
+static void train_finish(Learner* L, gbl_tree_result* result, gbl_split_record* records) {
+  if (!L->tree_pending) fatal("gbl_learner_train_finish: no tree in flight");
+  DeviceGuard guard(L->ds->device);
+  GBL_CUDA(cudaStreamSynchronize(L->stream));
+  L->tree_pending = false;
+  const TreeState& t = *L->ts_pinned;
+  const int ns = t.num_splits;
+  if (ns < 0 || ns > L->cfg.num_leaves - 1) fatal("learner: corrupt tree state (num_splits=%d)", ns);
+  const bool multi = L->comm != nullptr && L->comm->num_ranks > 1;
+  if (multi && ns > 0) {
+    // global leaf counts of every split (data_parallel_tree_learner.cpp:457-458): one all-reduce per tree
+    std::vector<long long> counts(2 * ns);
+    for (int k = 0; k < ns; ++k) {
+      counts[2 * k] = L->records_pinned[k].left_count;
+      counts[2 * k + 1] = L->records_pinned[k].right_count;
+    }
+    long long* buf = reinterpret_cast<long long*>(L->cand);  // >= 2*F*sizeof(BestSplit) bytes; reuse when it fits
+    long long* tmp = nullptr;
+    if (sizeof(long long) * 2 * ns > sizeof(BestSplit) * 2 * L->ds->num_features) {
+      GBL_CUDA(cudaMalloc(&tmp, sizeof(long long) * 2 * ns));
+      buf = tmp;
+    }
+    GBL_CUDA(cudaMemcpyAsync(buf, counts.data(), sizeof(long long) * 2 * ns, cudaMemcpyHostToDevice, L->stream));
+    comm_allreduce_i64(L->comm, buf, 2 * ns, RedOp::kSum, L->stream);
+    GBL_CUDA(cudaMemcpyAsync(counts.data(), buf, sizeof(long long) * 2 * ns, cudaMemcpyDeviceToHost, L->stream));
+    GBL_CUDA(cudaStreamSynchronize(L->stream));
+    if (tmp) cudaFree(tmp);
+    for (int k = 0; k < ns; ++k) {
+      L->records_pinned[k].left_count = static_cast<int>(counts[2 * k]);
+      L->records_pinned[k].right_count = static_cast<int>(counts[2 * k + 1]);
+    }
+  }
+  if (result != nullptr) {
+    std::memset(result, 0, sizeof(*result));
+    result->num_splits = ns;
+    result->root_output = t.root_output;
+    result->grad_scale = t.q_grad_scale;
+    result->hess_scale = t.q_hess_scale;
+  }
+  if (records != nullptr && ns > 0) std::memcpy(records, L->records_pinned, sizeof(gbl_split_record) * ns);
+}
+
+}  // namespace gbl
+
+using namespace gbl;
+
+#define LEARNER(h) (reinterpret_cast<Learner*>(h))
+
+extern "C" {
+
+int gbl_learner_create(const gbl_dataset* ds, const gbl_learner_config* config, gbl_comm* comm, gbl_learner** out) {
+  GBL_API_BEGIN();
+  if (out == nullptr) fatal("gbl_learner_create: null argument");
+  *out = reinterpret_cast<gbl_learner*>(
+      learner_create(reinterpret_cast<const Dataset*>(ds), config, reinterpret_cast<Comm*>(comm)));
+  GBL_API_END();
+}
+
+int gbl_learner_free(gbl_learner* learner) {
+  GBL_API_BEGIN();
+  learner_free(LEARNER(learner));
+  GBL_API_END();
+}
+
+int gbl_learner_reset_config(gbl_learner* learner, const gbl_learner_config* config) {
+  GBL_API_BEGIN();
+  Learner* L = LEARNER(learner);
+  if (L == nullptr || config == nullptr) fatal("gbl_learner_reset_config: null argument");
+  validate_config(*config);
+  DeviceGuard guard(L->ds->device);
+  GBL_CUDA(cudaStreamSynchronize(L->stream));
+  drop_graph(L);
+  const bool realloc = config->num_leaves != L->cfg.num_leaves || config->use_quantized_grad != L->cfg.use_quantized_grad;
+  L->cfg = *config;
+  if (realloc) {
+    free_tree_buffers(L);
+    alloc_tree_buffers(L);
+    L->has_tree = false;
+  } else {
+    L->dev.p = make_params(L);
+  }
+  GBL_API_END();
+}
+
+int gbl_learner_set_feature_mask(gbl_learner* learner, const int8_t* is_feature_used_host) {
+  GBL_API_BEGIN();
+  Learner* L = LEARNER(learner);
+  if (L == nullptr) fatal("gbl_learner_set_feature_mask: null learner");
+  DeviceGuard guard(L->ds->device);
+  GBL_CUDA(cudaStreamSynchronize(L->stream));
+  drop_graph(L);
+  if (is_feature_used_host == nullptr) {
+    cudaFree(L->feature_mask);
+    L->feature_mask = nullptr;
+  } else {
+    if (L->feature_mask == nullptr) GBL_CUDA(cudaMalloc(&L->feature_mask, L->ds->num_features));
+    GBL_CUDA(cudaMemcpy(L->feature_mask, is_feature_used_host, L->ds->num_features, cudaMemcpyHostToDevice));
+  }
+  GBL_API_END();
+}
+
+int gbl_learner_set_bagging_data(gbl_learner* learner, const int32_t* used_indices_host, int32_t num_used) {
+  GBL_API_BEGIN();
+  Learner* L = LEARNER(learner);
+  if (L == nullptr) fatal("gbl_learner_set_bagging_data: null learner");
+  DeviceGuard guard(L->ds->device);
+  GBL_CUDA(cudaStreamSynchronize(L->stream));
+  drop_graph(L);
+  if (used_indices_host == nullptr || num_used <= 0 || num_used >= L->ds->num_data) {
+    cudaFree(L->bag_indices);
+    L->bag_indices = nullptr;
+    L->bag_count = 0;
+  } else {
+    if (L->comm != nullptr && L->comm->num_ranks > 1) fatal("learner: bagging with the data-parallel learner is not supported");
+    if (L->cfg.use_quantized_grad) fatal("learner: bagging with use_quantized_grad is not supported");
+    if (L->bag_indices == nullptr) GBL_CUDA(cudaMalloc(&L->bag_indices, sizeof(int) * L->ds->num_data));
+    GBL_CUDA(cudaMemcpy(L->bag_indices, used_indices_host, sizeof(int) * num_used, cudaMemcpyHostToDevice));
+    L->bag_count = num_used;
+  }
+  GBL_API_END();
+}
+
+int gbl_learner_set_quant_random(gbl_learner* learner, const double* grad_random_host, const double* hess_random_host,
+                                 int64_t n) {
+  GBL_API_BEGIN();
+  Learner* L = LEARNER(learner);
+  if (L == nullptr || grad_random_host == nullptr || hess_random_host == nullptr) fatal("gbl_learner_set_quant_random: null argument");
+  if (n != L->ds->num_data) fatal("gbl_learner_set_quant_random: need num_data=%lld values", (long long)L->ds->num_data);
+  DeviceGuard guard(L->ds->device);
+  GBL_CUDA(cudaStreamSynchronize(L->stream));
+  drop_graph(L);
+  if (L->rand_g == nullptr) {
+    GBL_CUDA(cudaMalloc(&L->rand_g, sizeof(double) * n));
+    GBL_CUDA(cudaMalloc(&L->rand_h, sizeof(double) * n));
+  }
+  GBL_CUDA(cudaMemcpy(L->rand_g, grad_random_host, sizeof(double) * n, cudaMemcpyHostToDevice));
+  GBL_CUDA(cudaMemcpy(L->rand_h, hess_random_host, sizeof(double) * n, cudaMemcpyHostToDevice));
+  L->rand_n = n;
+  GBL_API_END();
+}
+
+int gbl_learner_set_quant_random_start(gbl_learner* learner, int32_t random_values_use_start) {
+  GBL_API_BEGIN();
+  Learner* L = LEARNER(learner);
+  if (L == nullptr) fatal("gbl_learner_set_quant_random_start: null learner");
+  L->rand_start = random_values_use_start;
+  GBL_API_END();
+}
+
+int gbl_learner_train_async(gbl_learner* learner, const float* gradients_dev, const float* hessians_dev) {
+  GBL_API_BEGIN();
+  Learner* L = LEARNER(learner);
+  if (L == nullptr) fatal("gbl_learner_train_async: null learner");
+  if (L->tree_pending) {
+    DeviceGuard guard(L->ds->device);
+    GBL_CUDA(cudaStreamSynchronize(L->stream));
+    L->tree_pending = false;
+  }
+  train_async(L, gradients_dev, hessians_dev);
+  GBL_API_END();
+}
+
+int gbl_learner_train_finish(gbl_learner* learner, gbl_tree_result* result_host, gbl_split_record* records_host) {
+  GBL_API_BEGIN();
+  Learner* L = LEARNER(learner);
+  if (L == nullptr) fatal("gbl_learner_train_finish: null learner");
+  train_finish(L, result_host, records_host);
+  GBL_API_END();
+}
+
+int gbl_learner_train(gbl_learner* learner, const float* gradients_dev, const float* hessians_dev,
+                      gbl_tree_result* result_host, gbl_split_record* records_host) {
+  GBL_API_BEGIN();
+  Learner* L = LEARNER(learner);
+  if (L == nullptr) fatal("gbl_learner_train: null learner");
+  train_async(L, gradients_dev, hessians_dev);
+  train_finish(L, result_host, records_host);
+  GBL_API_END();
+}
+
+int gbl_learner_train_host(gbl_learner* learner, const float* gradients_host, const float* hessians_host,
+                           gbl_tree_result* result_host, gbl_split_record* records_host) {
+  GBL_API_BEGIN();
+  Learner* L = LEARNER(learner);
+  if (L == nullptr || gradients_host == nullptr || hessians_host == nullptr) fatal("gbl_learner_train_host: null argument");
+  DeviceGuard guard(L->ds->device);
+  const size_t n = static_cast<size_t>(L->ds->num_data);
+  if (L->grad_stage == nullptr) {
+    GBL_CUDA(cudaMalloc(&L->grad_stage, sizeof(float) * n));
+    GBL_CUDA(cudaMalloc(&L->hess_stage, sizeof(float) * n));
+  }
+  GBL_CUDA(cudaMemcpyAsync(L->grad_stage, gradients_host, sizeof(float) * n, cudaMemcpyHostToDevice, L->stream));
+  GBL_CUDA(cudaMemcpyAsync(L->hess_stage, hessians_host, sizeof(float) * n, cudaMemcpyHostToDevice, L->stream));
+  train_async(L, L->grad_stage, L->hess_stage);
+  train_finish(L, result_host, records_host);
+  GBL_API_END();
+}
+
+int gbl_learner_add_prediction_to_score(gbl_learner* learner, const double* leaf_values_host, int32_t num_leaves,
+                                        double* score_dev) {
+  GBL_API_BEGIN();
+  Learner* L = LEARNER(learner);
+  if (L == nullptr || leaf_values_host == nullptr || score_dev == nullptr) fatal("gbl_learner_add_prediction_to_score: null argument");
+  if (!L->has_tree) fatal("gbl_learner_add_prediction_to_score: no tree trained yet");
+  if (num_leaves < 1 || num_leaves > L->cfg.num_leaves) fatal("gbl_learner_add_prediction_to_score: bad num_leaves");
+  DeviceGuard guard(L->ds->device);
+  GBL_CUDA(cudaMemcpyAsync(L->leaf_values_tmp, leaf_values_host, sizeof(double) * num_leaves, cudaMemcpyHostToDevice, L->stream));
+  launch_add_score(L->dev, L->leaf_values_tmp, 1.0, 0.0, score_dev, L->stream);
+  GBL_CUDA(cudaStreamSynchronize(L->stream));
+  GBL_API_END();
+}
+
+int gbl_learner_add_prediction_to_score_dev(gbl_learner* learner, double shrinkage, double bias, double* score_dev) {
+  GBL_API_BEGIN();
+  Learner* L = LEARNER(learner);
+  if (L == nullptr || score_dev == nullptr) fatal("gbl_learner_add_prediction_to_score_dev: null argument");
+  if (!L->has_tree) fatal("gbl_learner_add_prediction_to_score_dev: no tree trained yet");
+  DeviceGuard guard(L->ds->device);
+  launch_add_score(L->dev, L->leaf_values, shrinkage, bias, score_dev, L->stream);
+  GBL_API_END();
+}
+
+int gbl_learner_get_leaf_assignment(gbl_learner* learner, int32_t* out_host) {
+  GBL_API_BEGIN();
+  Learner* L = LEARNER(learner);
+  if (L == nullptr || out_host == nullptr) fatal("gbl_learner_get_leaf_assignment: null argument");
+  if (!L->has_tree) fatal("gbl_learner_get_leaf_assignment: no tree trained yet");
+  DeviceGuard guard(L->ds->device);
+  const size_t n = static_cast<size_t>(L->ds->num_data);
+  int* tmp = nullptr;
+  GBL_CUDA(cudaMalloc(&tmp, sizeof(int) * n));
+  GBL_CUDA(cudaMemsetAsync(tmp, 0xff, sizeof(int) * n, L->stream));
+  launch_leaf_assignment(L->dev, tmp, L->stream);
+  GBL_CUDA(cudaMemcpyAsync(out_host, tmp, sizeof(int) * n, cudaMemcpyDeviceToHost, L->stream));
+  GBL_CUDA(cudaStreamSynchronize(L->stream));
+  cudaFree(tmp);
+  GBL_API_END();
+}
+
+int gbl_learner_get_leaf_indices(gbl_learner* learner, int32_t leaf, int32_t* out_host, int32_t* out_count) {
+  GBL_API_BEGIN();
+  Learner* L = LEARNER(learner);
+  if (L == nullptr || out_count == nullptr) fatal("gbl_learner_get_leaf_indices: null argument");
+  if (!L->has_tree) fatal("gbl_learner_get_leaf_indices: no tree trained yet");
+  if (leaf < 0 || leaf >= L->cfg.num_leaves) fatal("gbl_learner_get_leaf_indices: leaf out of range");
+  DeviceGuard guard(L->ds->device);
+  GBL_CUDA(cudaStreamSynchronize(L->stream));
+  LeafState ls;
+  GBL_CUDA(cudaMemcpy(&ls, L->leaves + leaf, sizeof(LeafState), cudaMemcpyDeviceToHost));
+  *out_count = ls.count;
+  if (out_host != nullptr && ls.count > 0)
+    GBL_CUDA(cudaMemcpy(out_host, L->idx[ls.buf] + ls.begin, sizeof(int) * ls.count, cudaMemcpyDeviceToHost));
+  GBL_API_END();
+}
+
+int gbl_learner_get_histogram(gbl_learner* learner, int32_t leaf, int32_t feature, double* out_host) {
+  GBL_API_BEGIN();
+  Learner* L = LEARNER(learner);
+  if (L == nullptr || out_host == nullptr) fatal("gbl_learner_get_histogram: null argument");
+  if (!L->has_tree) fatal("gbl_learner_get_histogram: no tree trained yet");
+  if (leaf < 0 || leaf >= L->cfg.num_leaves || feature < 0 || feature >= L->ds->num_features)
+    fatal("gbl_learner_get_histogram: index out of range");
+  DeviceGuard guard(L->ds->device);
+  GBL_CUDA(cudaStreamSynchronize(L->stream));
+  LeafState ls;
+  GBL_CUDA(cudaMemcpy(&ls, L->leaves + leaf, sizeof(LeafState), cudaMemcpyDeviceToHost));
+  TreeState ts;
+  GBL_CUDA(cudaMemcpy(&ts, L->ts, sizeof(TreeState), cudaMemcpyDeviceToHost));
+  const long long words = L->dev.slot_stride;
+  std::vector<long long> slot(words);
+  GBL_CUDA(cudaMemcpy(slot.data(), L->hist_pool + static_cast<long long>(ls.slot) * words, sizeof(long long) * words,
+                      cudaMemcpyDeviceToHost));
+  const int tile = feature / kTile, fl = feature % kTile;
+  const int nb = L->ds->meta_host[feature].num_bin;
+  for (int b = 0; b < nb; ++b) {
+    const long long e = (static_cast<long long>(tile) * kMaxBin + b) * kTile + fl;
+    if (L->cfg.use_quantized_grad) {
+      const long long v = slot[e];
+      out_host[2 * b] = static_cast<double>(static_cast<int>(v >> 32));
+      out_host[2 * b + 1] = static_cast<double>(static_cast<unsigned>(v & 0xffffffffLL));
+    } else {
+      out_host[2 * b] = static_cast<double>(slot[2 * e]) * ts.g_inv;
+      out_host[2 * b + 1] = static_cast<double>(slot[2 * e + 1]) * ts.h_inv;
+    }
+  }
+  GBL_API_END();
+}
+
+int gbl_learner_get_discretized(gbl_learner* learner, int8_t* out_host) {
+  GBL_API_BEGIN();
+  Learner* L = LEARNER(learner);
+  if (L == nullptr || out_host == nullptr) fatal("gbl_learner_get_discretized: null argument");
+  if (!L->has_tree || !L->cfg.use_quantized_grad) fatal("gbl_learner_get_discretized: no quantized tree trained yet");
+  DeviceGuard guard(L->ds->device);
+  GBL_CUDA(cudaStreamSynchronize(L->stream));
+  GBL_CUDA(cudaMemcpy(out_host, L->gh_q, sizeof(short) * L->ds->num_data, cudaMemcpyDeviceToHost));
+  GBL_API_END();
+}
+
+int gbl_learner_histogram_words(gbl_learner* learner, int64_t* out_words) {
+  GBL_API_BEGIN();
+  Learner* L = LEARNER(learner);
+  if (L == nullptr || out_words == nullptr) fatal("gbl_learner_histogram_words: null argument");
+  *out_words = L->dev.slot_stride;
+  GBL_API_END();
+}
+
+int gbl_learner_construct_histogram(gbl_learner* learner, const int32_t* indices_dev, int64_t num_indices,
+                                    int64_t* out_hist_dev) {
+  GBL_API_BEGIN();
+  Learner* L = LEARNER(learner);
+  if (L == nullptr || out_hist_dev == nullptr) fatal("gbl_learner_construct_histogram: null argument");
+  if (!L->has_tree) fatal("gbl_learner_construct_histogram: train one tree first (gradients are taken from it)");
+  if (num_indices < 0 || num_indices > L->ds->num_data) fatal("gbl_learner_construct_histogram: bad num_indices");
+  DeviceGuard guard(L->ds->device);
+  launch_histogram(L->dev, 0, indices_dev, static_cast<int>(num_indices), reinterpret_cast<long long*>(out_hist_dev),
+                   L->stream);
+  GBL_API_END();
+}
+
+void* gbl_learner_stream(gbl_learner* learner) { return learner ? LEARNER(learner)->stream : nullptr; }
+
+}  // extern "C"

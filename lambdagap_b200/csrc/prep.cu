@@ -1,0 +1,188 @@
+// prep.cu -- per-tree preparation kernels: DataPartition::Init, gradient range scan, fixed-point conversion
+// (float mode) and GradientDiscretizer::DiscretizeGradients (quantized mode).
+//
+// Reference: src/treelearner/data_partition.hpp:49-64 (iota / bagged indices),
+//            src/treelearner/gradient_discretizer.cpp:68-161 (max |g|, max |h|, scales, int8 rounding).
+#include "kernels.cuh"
+
+namespace gbl {
+
+__global__ void __launch_bounds__(256) iota_kernel(int* __restrict__ out, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = i;
+}
+
+__global__ void __launch_bounds__(256) copy_int_kernel(int* __restrict__ out, const int* __restrict__ in, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = in[i];
+}
+
+// One CTA: resets TreeState / LeafState for a new tree (SerialTreeLearner::BeforeTrain,
+// src/treelearner/serial_tree_learner.cpp:288-338).
+__global__ void __launch_bounds__(256) tree_begin_kernel(LearnerDev d, int root_count) {
+  const int tid = threadIdx.x;
+  for (int l = tid; l < d.p.num_leaves; l += blockDim.x) {
+    LeafState& L = d.leaves[l];
+    L.begin = 0;
+    L.count = 0;
+    L.global_count = 0;
+    L.depth = 0;
+    L.buf = 0;
+    L.slot = l;
+    L.sum_g = 0.0;
+    L.sum_h = 0.0;
+    L.ig = 0;
+    L.ih = 0;
+    L.output = 0.0;
+    L.best.gain = -INFINITY;  // SplitInfo::Reset (split_info.hpp:132-136)
+    L.best.feature = -1;
+    L.best.real_feature = -1;
+    d.leaf_values[l] = 0.0;
+  }
+  // FeatureHistogram::is_splittable_ of the root slot starts true (feature_histogram.hpp:1356)
+  for (int f = tid; f < d.p.num_features; f += blockDim.x) d.splittable[f] = 1;
+  __syncthreads();
+  if (tid == 0) {
+    TreeState& t = *d.ts;
+    t.num_leaves_cur = 1;
+    t.done = 0;
+    t.num_splits = 0;
+    t.smaller = 0;
+    t.larger = -1;
+    t.skip_hist = 0;
+    t.do_split = 0;
+    t.split_leaf = -1;
+    t.scan_done_counter = 0;
+    t.part_done_counter = 0;
+    t.part_ticket = 0;
+    t.max_abs_g = 0.f;
+    t.max_abs_h = 0.f;
+    t.root_output = 0.0;
+    d.leaves[0].count = root_count;
+    d.leaves[0].global_count = root_count;
+    // data-parallel: the local root count rides in the tail of slot 0 through the histogram all-reduce
+    d.hist_pool[d.slot_stride - kTailWords + 0] = root_count;
+    d.hist_pool[d.slot_stride - kTailWords + 1] = 0;
+  }
+}
+
+// max |g|, max |h| over all rows (gradient_discretizer.cpp:72-100).  Non-negative floats order like their bit
+// patterns, so atomicMax on the int view is exact.
+__global__ void __launch_bounds__(256) maxabs_kernel(const float* __restrict__ g, const float* __restrict__ h, int n,
+                                                     TreeState* ts) {
+  float mg = 0.f, mh = 0.f;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    mg = fmaxf(mg, fabsf(g[i]));
+    mh = fmaxf(mh, fabsf(h[i]));
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    mg = fmaxf(mg, __shfl_xor_sync(0xffffffffu, mg, o));
+    mh = fmaxf(mh, __shfl_xor_sync(0xffffffffu, mh, o));
+  }
+  __shared__ float sg[8], sh[8];
+  if ((threadIdx.x & 31) == 0) {
+    sg[threadIdx.x >> 5] = mg;
+    sh[threadIdx.x >> 5] = mh;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < 8; ++w) {
+      mg = fmaxf(mg, sg[w]);
+      mh = fmaxf(mh, sh[w]);
+    }
+    atomicMax(reinterpret_cast<int*>(&ts->max_abs_g), __float_as_int(mg));
+    atomicMax(reinterpret_cast<int*>(&ts->max_abs_h), __float_as_int(mh));
+  }
+}
+
+__device__ inline double pow2_scale_for(float max_abs) {
+  if (!(max_abs > 0.f) || isinf(max_abs)) return 1.0;
+  const int e = ilogbf(max_abs) + 1;  // max_abs = m * 2^e, m in [0.5, 1)
+  return ldexp(1.0, 30 - e);          // |v| * scale <= 2^30
+}
+
+__global__ void scales_kernel(LearnerDev d) {
+  TreeState& t = *d.ts;
+  if (d.p.quantized) {
+    // gradient_discretizer.cpp:105-114
+    const double max_g = static_cast<double>(t.max_abs_g);
+    const double max_h = static_cast<double>(t.max_abs_h);
+    t.q_grad_scale = max_g / static_cast<double>(d.p.num_grad_quant_bins / 2);
+    t.q_hess_scale = d.p.is_constant_hessian ? max_h : max_h / static_cast<double>(d.p.num_grad_quant_bins);
+    t.q_inv_grad_scale = 1.0 / t.q_grad_scale;
+    t.q_inv_hess_scale = 1.0 / t.q_hess_scale;
+  } else {
+    t.g_scale = pow2_scale_for(t.max_abs_g);
+    t.h_scale = pow2_scale_for(t.max_abs_h);
+    t.g_inv = 1.0 / t.g_scale;
+    t.h_inv = 1.0 / t.h_scale;
+  }
+}
+
+// float mode: exact power-of-two fixed point, |value| <= 2^30
+__global__ void __launch_bounds__(256) to_fixed_kernel(LearnerDev d) {
+  const double gs = d.ts->g_scale, hs = d.ts->h_scale;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < d.num_data; i += gridDim.x * blockDim.x) {
+    int2 v;
+    v.x = __double2int_rn(static_cast<double>(d.grad[i]) * gs);
+    v.y = __double2int_rn(static_cast<double>(d.hess[i]) * hs);
+    d.gh_fix[i] = v;
+  }
+}
+
+// GradientDiscretizer::DiscretizeGradients, gradient_discretizer.cpp:116-160.  Casts truncate toward zero.
+__global__ void __launch_bounds__(256) discretize_kernel(LearnerDev d) {
+  const double ig = d.ts->q_inv_grad_scale, ih = d.ts->q_inv_hess_scale;
+  const int n = d.num_data;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const double gradient = static_cast<double>(d.grad[i]);
+    double rg = 0.5, rh = 0.5;
+    if (d.rand_g != nullptr) {
+      const int pos = static_cast<int>((static_cast<long long>(i) + d.rand_start) % n);
+      rg = d.rand_g[pos];
+      rh = d.rand_h[pos];
+    }
+    const signed char qg = gradient >= 0.0 ? static_cast<signed char>(static_cast<int>(gradient * ig + rg))
+                                            : static_cast<signed char>(static_cast<int>(gradient * ig - rg));
+    signed char qh;
+    if (d.p.is_constant_hessian) {
+      qh = 1;
+    } else {
+      qh = static_cast<signed char>(static_cast<int>(static_cast<double>(d.hess[i]) * ih + rh));
+    }
+    // low byte = hess, high byte = grad (int8 pair read as one int16, dense_bin.hpp:181,196)
+    d.gh_q[i] = static_cast<short>((static_cast<int>(qg) << 8) | (static_cast<int>(qh) & 0xff));
+  }
+}
+
+void launch_iota(int* out, int n, cudaStream_t s) {
+  GBL_LAUNCH(iota_kernel, (n + 255) / 256, 256, 0, s, out, n);
+}
+
+void launch_tree_begin(const LearnerDev& d, const int* bag_indices, int bag_count, cudaStream_t s) {
+  const int root_count = bag_indices != nullptr ? bag_count : d.num_data;
+  GBL_LAUNCH(tree_begin_kernel, 1, 256, 0, s, d, root_count);
+  if (bag_indices != nullptr) {
+    GBL_LAUNCH(copy_int_kernel, (bag_count + 255) / 256, 256, 0, s, d.idx[0], bag_indices, bag_count);
+  } else {
+    launch_iota(d.idx[0], d.num_data, s);
+  }
+}
+
+void launch_maxabs(const LearnerDev& d, cudaStream_t s) {
+  const int grid = std::min((d.num_data + 255) / 256, kNumSM * 8);
+  GBL_LAUNCH(maxabs_kernel, grid, 256, 0, s, d.grad, d.hess, d.num_data, d.ts);
+}
+
+void launch_scales_and_convert(const LearnerDev& d, cudaStream_t s) {
+  GBL_LAUNCH(scales_kernel, 1, 1, 0, s, d);
+  const int grid = std::min((d.num_data + 255) / 256, kNumSM * 8);
+  if (d.p.quantized) {
+    GBL_LAUNCH(discretize_kernel, grid, 256, 0, s, d);
+  } else {
+    GBL_LAUNCH(to_fixed_kernel, grid, 256, 0, s, d);
+  }
+}
+
+}  // namespace gbl
