@@ -21,10 +21,25 @@
 
 namespace gbl {
 
-constexpr int kHistThreadsQ = 256;
-constexpr int kHistThreadsF = 512;
-constexpr int kMinChunk = 2048;  // rows per CTA below which fewer CTAs are used
-constexpr int kUnroll = 8;
+constexpr int kHistThreads = 1024;
+constexpr int kHistWarps = kHistThreads / 32;
+constexpr int kMinChunk = 1024;   // rows per CTA below which fewer CTAs are used
+constexpr int kPlane = kMaxBin * kTile;  // words per smem plane
+
+// Non-returning shared-memory atomic add on a 32-bit shared-window address (SASS: ATOMS.ADD RZ).
+__device__ __forceinline__ void red_shared_add(unsigned addr, int v) {
+  asm volatile("red.shared.add.s32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+// Hides where a value came from so that ptxas keeps it in one register (pair) instead of re-deriving it from
+// uniform + per-lane parts on every use (keeps the per-row address math at one IMAD.WIDE / one LEA).
+__device__ __forceinline__ const uint8_t* opaque_ptr(const uint8_t* p) {
+  asm volatile("" : "+l"(p));
+  return p;
+}
+__device__ __forceinline__ unsigned opaque_u32(unsigned v) {
+  asm volatile("" : "+r"(v));
+  return v;
+}
 
 struct HistJob {
   const int* indices;  // nullptr -> identity
@@ -62,67 +77,71 @@ __device__ inline int chunk_rows(int n, int grid_x, int cap) {
 }
 
 // ------------------------------------------------------------------------------------------ quantized mode
-// smem: int32 [256 bins][32 lanes]
-__global__ void __launch_bounds__(kHistThreadsQ) hist_quant_kernel(LearnerDev d, long long* __restrict__ out,
-                                                                   const int* explicit_indices, int explicit_count,
-                                                                   int flush_cap) {
+// smem: int32 hist[256 bins][32 lanes] + per-warp staging of 32 rows {row, packed (grad << 16) + hess}.
+// Hot loop per row and warp: LDS.64 (row info, broadcast) + LDG.U8 (32 bins = one sector) + ATOMS.ADD.
+__global__ void __launch_bounds__(kHistThreads, 1) hist_quant_kernel(LearnerDev d, long long* __restrict__ out,
+                                                                     const int* explicit_indices, int explicit_count,
+                                                                     int flush_cap) {
   extern __shared__ int sh[];
+  int2* stage_all = reinterpret_cast<int2*>(sh + kPlane);
   const HistJob job = resolve_job(d, explicit_indices, explicit_count);
   if (job.count == 0) return;
   const int tile = blockIdx.y;
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
-  constexpr int kWarps = kHistThreadsQ / 32;
-  const bool lane_active = tile * kTile + lane < d.p.num_features;
   const int chunk = chunk_rows(job.count, gridDim.x, flush_cap);
   const int num_chunks = (job.count + chunk - 1) / chunk;
   if (static_cast<int>(blockIdx.x) >= num_chunks) return;
 
-  for (int e = threadIdx.x; e < kMaxBin * kTile; e += kHistThreadsQ) sh[e] = 0;
+  for (int e = threadIdx.x; e < kPlane; e += kHistThreads) sh[e] = 0;
   __syncthreads();
 
-  const uint8_t* __restrict__ rp = d.row_bins + tile * kTile + lane;
-  const int64_t rs = d.row_stride;
-  long long* __restrict__ dst = out + static_cast<long long>(tile) * kMaxBin * kTile;
+  const uint8_t* rp = opaque_ptr(d.row_bins + tile * kTile + lane);
+  const unsigned rs = static_cast<unsigned>(d.row_stride);
+  int2* st = stage_all + warp * 32;
+  const unsigned col = opaque_u32(static_cast<unsigned>(__cvta_generic_to_shared(sh + lane)));
+  const int lanes_used = min(kTile, d.p.num_features - tile * kTile);
+  long long* __restrict__ dst = out + static_cast<long long>(tile) * kPlane;
 
   for (int c = blockIdx.x; c < num_chunks; c += gridDim.x) {
     const int c_begin = c * chunk;
     const int c_end = min(job.count, c_begin + chunk);
-    for (int base = c_begin + warp * 32; base < c_end; base += kWarps * 32) {
+    for (int base = c_begin + warp * 32; base < c_end; base += kHistWarps * 32) {
       const int my = base + lane;
-      int r = -1;
-      int v = 0;
+      int2 t = make_int2(0, 0);  // padding rows add 0 to bin(row 0)
       if (my < c_end) {
-        r = job.indices != nullptr ? job.indices[job.begin + my] : my;
-        const int q = d.gh_q[r];                  // int16: high byte grad (signed), low byte hess
-        v = ((q >> 8) << 16) + (q & 0xff);        // packed (grad << 16) + hess
+        const int r = job.indices != nullptr ? job.indices[job.begin + my] : my;
+        const int q = d.gh_q[r];                           // int16: high byte grad (signed), low byte hess
+        t = make_int2(r, ((q >> 8) << 16) + (q & 0xff));   // packed (grad << 16) + hess
       }
-      const int rows = min(32, c_end - base);
-      for (int j0 = 0; j0 < rows; j0 += kUnroll) {
-        int bins[kUnroll];
-        int vals[kUnroll];
+      st[lane] = t;
+      __syncwarp();
 #pragma unroll
-        for (int u = 0; u < kUnroll; ++u) {
-          const int rj = __shfl_sync(0xffffffffu, r, (j0 + u) & 31);
-          vals[u] = __shfl_sync(0xffffffffu, v, (j0 + u) & 31);
-          const bool ok = (j0 + u < rows);
-          bins[u] = ok ? static_cast<int>(rp[static_cast<int64_t>(rj) * rs]) : -1;
+      for (int j0 = 0; j0 < 32; j0 += 16) {
+        int bins[16];
+        int vals[16];
+#pragma unroll
+        for (int u = 0; u < 16; ++u) {
+          const int2 q = st[j0 + u];
+          vals[u] = q.y;
+          bins[u] = __ldg(rp + static_cast<size_t>(static_cast<unsigned>(q.x)) * rs);
         }
 #pragma unroll
-        for (int u = 0; u < kUnroll; ++u) {
-          if (bins[u] >= 0 && lane_active && vals[u] != 0) atomicAdd(&sh[bins[u] * kTile + lane], vals[u]);
-        }
+        for (int u = 0; u < 16; ++u) red_shared_add(col + bins[u] * (kTile * 4), vals[u]);
       }
+      __syncwarp();
     }
     __syncthreads();
     // flush + re-zero: widen (g16 | h16) to the reference's (g32 | h32) packing
-    for (int e = threadIdx.x; e < kMaxBin * kTile; e += kHistThreadsQ) {
+    for (int e = threadIdx.x; e < kPlane; e += kHistThreads) {
       const int s = sh[e];
       if (s != 0) {
-        const long long g = static_cast<long long>(s >> 16);
-        const long long h = static_cast<long long>(s & 0xffff);
-        atomicAdd(reinterpret_cast<unsigned long long*>(dst + e), static_cast<unsigned long long>((g << 32) + h));
         sh[e] = 0;
+        if ((e & 31) < lanes_used) {
+          const long long g = static_cast<long long>(s >> 16);
+          const long long h = static_cast<long long>(s & 0xffff);
+          atomicAdd(reinterpret_cast<unsigned long long*>(dst + e), static_cast<unsigned long long>((g << 32) + h));
+        }
       }
     }
     __syncthreads();
@@ -130,84 +149,90 @@ __global__ void __launch_bounds__(kHistThreadsQ) hist_quant_kernel(LearnerDev d,
 }
 
 // ------------------------------------------------------------------------------------------ float mode
-// smem: 4 planes of int32 [256][32]: g_lo, g_hi, h_lo, h_hi
-__global__ void __launch_bounds__(kHistThreadsF) hist_float_kernel(LearnerDev d, long long* __restrict__ out,
-                                                                   const int* explicit_indices, int explicit_count) {
+// smem: 4 planes of int32 [256][32]: g_lo, g_hi, h_lo, h_hi (16-bit limbs of the 2^k fixed-point value, so no
+// carries are needed: lo limbs sum < 2^16 * 65536 rows, hi limbs < 2^15 * 65536 rows) + per-warp staging.
+// Hot loop per row and warp: LDS.128 + LDG.U8 + 4 ATOMS.ADD.
+constexpr int kFloatFlushCap = 65536;
+
+__global__ void __launch_bounds__(kHistThreads, 1) hist_float_kernel(LearnerDev d, long long* __restrict__ out,
+                                                                     const int* explicit_indices, int explicit_count) {
   extern __shared__ int sh[];
-  unsigned* __restrict__ g_lo = reinterpret_cast<unsigned*>(sh);
-  int* __restrict__ g_hi = sh + kMaxBin * kTile;
-  unsigned* __restrict__ h_lo = reinterpret_cast<unsigned*>(sh + 2 * kMaxBin * kTile);
-  int* __restrict__ h_hi = sh + 3 * kMaxBin * kTile;
+  int4* stage_all = reinterpret_cast<int4*>(sh + 4 * kPlane);
   const HistJob job = resolve_job(d, explicit_indices, explicit_count);
   if (job.count == 0) return;
   const int tile = blockIdx.y;
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
-  constexpr int kWarps = kHistThreadsF / 32;
-  const bool lane_active = tile * kTile + lane < d.p.num_features;
-  const int chunk = chunk_rows(job.count, gridDim.x, 1 << 30);
+  const int chunk = chunk_rows(job.count, gridDim.x, kFloatFlushCap);
   const int num_chunks = (job.count + chunk - 1) / chunk;
   if (static_cast<int>(blockIdx.x) >= num_chunks) return;
 
-  for (int e = threadIdx.x; e < 4 * kMaxBin * kTile; e += kHistThreadsF) sh[e] = 0;
+  for (int e = threadIdx.x; e < 4 * kPlane; e += kHistThreads) sh[e] = 0;
   __syncthreads();
 
-  const uint8_t* __restrict__ rp = d.row_bins + tile * kTile + lane;
-  const int64_t rs = d.row_stride;
+  const uint8_t* rp = opaque_ptr(d.row_bins + tile * kTile + lane);
+  const unsigned rs = static_cast<unsigned>(d.row_stride);
+  int4* st = stage_all + warp * 32;
+  const unsigned col = opaque_u32(static_cast<unsigned>(__cvta_generic_to_shared(sh + lane)));
+  const int lanes_used = min(kTile, d.p.num_features - tile * kTile);
+  longlong2* __restrict__ dst = reinterpret_cast<longlong2*>(out) + static_cast<long long>(tile) * kPlane;
 
   for (int c = blockIdx.x; c < num_chunks; c += gridDim.x) {
     const int c_begin = c * chunk;
     const int c_end = min(job.count, c_begin + chunk);
-    for (int base = c_begin + warp * 32; base < c_end; base += kWarps * 32) {
+    for (int base = c_begin + warp * 32; base < c_end; base += kHistWarps * 32) {
       const int my = base + lane;
-      int r = -1;
-      int2 v = make_int2(0, 0);
+      int4 t = make_int4(0, 0, 0, 0);
       if (my < c_end) {
-        r = job.indices != nullptr ? job.indices[job.begin + my] : my;
-        v = d.gh_fix[r];
+        const int r = job.indices != nullptr ? job.indices[job.begin + my] : my;
+        const int2 v = d.gh_fix[r];
+        t = make_int4(r, v.x, v.y, 0);
       }
-      const int rows = min(32, c_end - base);
-      for (int j0 = 0; j0 < rows; j0 += kUnroll) {
-        int bins[kUnroll];
-        int gv[kUnroll];
-        int hv[kUnroll];
+      st[lane] = t;
+      __syncwarp();
 #pragma unroll
-        for (int u = 0; u < kUnroll; ++u) {
-          const int rj = __shfl_sync(0xffffffffu, r, (j0 + u) & 31);
-          gv[u] = __shfl_sync(0xffffffffu, v.x, (j0 + u) & 31);
-          hv[u] = __shfl_sync(0xffffffffu, v.y, (j0 + u) & 31);
-          const bool ok = (j0 + u < rows);
-          bins[u] = ok ? static_cast<int>(rp[static_cast<int64_t>(rj) * rs]) : -1;
+      for (int j0 = 0; j0 < 32; j0 += 8) {
+        int bins[8];
+        int gv[8];
+        int hv[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const int4 q = st[j0 + u];
+          gv[u] = q.y;
+          hv[u] = q.z;
+          bins[u] = __ldg(rp + static_cast<size_t>(static_cast<unsigned>(q.x)) * rs);
         }
 #pragma unroll
-        for (int u = 0; u < kUnroll; ++u) {
-          if (bins[u] >= 0 && lane_active) {
-            const int a = bins[u] * kTile + lane;
-            const unsigned gl = static_cast<unsigned>(gv[u]);
-            const unsigned og = atomicAdd(&g_lo[a], gl);
-            const int gd = (gv[u] >> 31) + ((og + gl) < og ? 1 : 0);  // sign extension + carry
-            if (gd != 0) atomicAdd(&g_hi[a], gd);
-            const unsigned hl = static_cast<unsigned>(hv[u]);
-            const unsigned oh = atomicAdd(&h_lo[a], hl);
-            const int hd = (hv[u] >> 31) + ((oh + hl) < oh ? 1 : 0);
-            if (hd != 0) atomicAdd(&h_hi[a], hd);
-          }
+        for (int u = 0; u < 8; ++u) {
+          const unsigned a = col + bins[u] * (kTile * 4);
+          red_shared_add(a, gv[u] & 0xffff);
+          red_shared_add(a + kPlane * 4, gv[u] >> 16);
+          red_shared_add(a + 2 * kPlane * 4, hv[u] & 0xffff);
+          red_shared_add(a + 3 * kPlane * 4, hv[u] >> 16);
         }
       }
+      __syncwarp();
     }
-  }
-  __syncthreads();
-  longlong2* __restrict__ dst = reinterpret_cast<longlong2*>(out) + static_cast<long long>(tile) * kMaxBin * kTile;
-  for (int e = threadIdx.x; e < kMaxBin * kTile; e += kHistThreadsF) {
-    const long long g = (static_cast<long long>(g_hi[e]) << 32) + static_cast<long long>(g_lo[e]);
-    const long long h = (static_cast<long long>(h_hi[e]) << 32) + static_cast<long long>(h_lo[e]);
-    if (g != 0) atomicAdd(reinterpret_cast<unsigned long long*>(&dst[e].x), static_cast<unsigned long long>(g));
-    if (h != 0) atomicAdd(reinterpret_cast<unsigned long long*>(&dst[e].y), static_cast<unsigned long long>(h));
+    __syncthreads();
+    for (int e = threadIdx.x; e < kPlane; e += kHistThreads) {
+      const long long g = (static_cast<long long>(sh[e + kPlane]) << 16) + static_cast<long long>(static_cast<unsigned>(sh[e]));
+      const long long h =
+          (static_cast<long long>(sh[e + 3 * kPlane]) << 16) + static_cast<long long>(static_cast<unsigned>(sh[e + 2 * kPlane]));
+      if ((e & 31) < lanes_used) {
+        if (g != 0) atomicAdd(reinterpret_cast<unsigned long long*>(&dst[e].x), static_cast<unsigned long long>(g));
+        if (h != 0) atomicAdd(reinterpret_cast<unsigned long long*>(&dst[e].y), static_cast<unsigned long long>(h));
+      }
+      sh[e] = 0;
+      sh[e + kPlane] = 0;
+      sh[e + 2 * kPlane] = 0;
+      sh[e + 3 * kPlane] = 0;
+    }
+    __syncthreads();
   }
 }
 
-static const int kSmemQ = kMaxBin * kTile * 4;       // 32 KB
-static const int kSmemF = 4 * kMaxBin * kTile * 4;   // 128 KB
+static const int kSmemQ = kPlane * 4 + kHistWarps * 32 * 8;        // 32 KB + 8 KB staging
+static const int kSmemF = 4 * kPlane * 4 + kHistWarps * 32 * 16;   // 128 KB + 16 KB staging
 
 void histogram_setup() {
   GBL_CUDA(cudaFuncSetAttribute(hist_float_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemF));
@@ -222,12 +247,12 @@ void launch_histogram(const LearnerDev& d, int slot, const int* explicit_indices
     // 16-bit halves hold sums of at most flush_cap rows: |g| <= bins/2, h <= bins (gradient_discretizer.cpp:105-127)
     int flush_cap = (65535 / std::max(1, d.p.num_grad_quant_bins)) & ~255;
     flush_cap = std::max(256, std::min(flush_cap, 1 << 20));
-    const int gx = std::max(1, (kNumSM * 6 + tiles - 1) / tiles);
-    GBL_LAUNCH(hist_quant_kernel, dim3(gx, tiles), kHistThreadsQ, kSmemQ, s, d, out, explicit_indices, explicit_count,
+    const int gx = std::max(1, (kNumSM + tiles - 1) / tiles);
+    GBL_LAUNCH(hist_quant_kernel, dim3(gx, tiles), kHistThreads, kSmemQ, s, d, out, explicit_indices, explicit_count,
                flush_cap);
   } else {
     const int gx = std::max(1, (kNumSM + tiles - 1) / tiles);
-    GBL_LAUNCH(hist_float_kernel, dim3(gx, tiles), kHistThreadsF, kSmemF, s, d, out, explicit_indices, explicit_count);
+    GBL_LAUNCH(hist_float_kernel, dim3(gx, tiles), kHistThreads, kSmemF, s, d, out, explicit_indices, explicit_count);
   }
 }
 

@@ -41,6 +41,8 @@ for t in range(trees):
     res, recs = lrn.train(gbuf, hbuf)
     dt = time.time() - t0
     print("tree %d: %.2f ms, splits=%d launches=%d" % (t, dt * 1e3, res["num_splits"], capi.kernel_launch_count() - l0), flush=True)
+    sizes = [n] + [min(r["left_count"], r["right_count"]) for r in recs]
+    print("hist_rows", " ".join(str(x) for x in sizes[:len(recs)]), flush=True)
     assign = lrn.leaf_assignment()
     vals = np.zeros(leaves)
     vals[0] = res["root_output"]
