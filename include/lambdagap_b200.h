@@ -200,6 +200,23 @@ GBL_API int gbl_learner_construct_histogram(gbl_learner* learner, const int32_t*
                                             int64_t* out_hist_dev);
 GBL_API void* gbl_learner_stream(gbl_learner* learner);
 
+/* Per-stage device time of the trees trained since profiling was switched on, measured with CUDA events on the
+ * learner's stream around every kernel group (profiling disables CUDA-graph replay and adds two event records
+ * per stage and round).  Feeds bench.py's `roofline` object; the reference's analogue is the USE_TIMETAG
+ * stage table (include/LightGBM/utils/common.h:984-1068). */
+typedef struct gbl_profile {
+  double hist_ms;        /* ConstructHistograms */
+  double find_ms;        /* FindBestSplitsFromHistograms (+ arg-max) */
+  double partition_ms;   /* DataPartition::Split + bookkeeping */
+  double other_ms;       /* BeforeTrain, gradient preparation, root sums */
+  double collective_ms;  /* NCCL all-reduces (data-parallel learner) */
+  int64_t hist_launches; /* histogram kernel launches that had rows to process */
+  int64_t hist_rows;     /* sum of leaf rows over those launches */
+  int64_t trees;
+} gbl_profile;
+GBL_API int gbl_learner_set_profiling(gbl_learner* learner, int32_t enabled);
+GBL_API int gbl_learner_get_profile(gbl_learner* learner, gbl_profile* out, int32_t reset);
+
 /* ---------------------------------------------------------------- src/objective */
 typedef struct gbl_objective_config {
   int32_t kind;                        /* GBL_OBJ_* */

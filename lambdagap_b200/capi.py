@@ -50,6 +50,12 @@ class TreeResult(ctypes.Structure):
                 ("grad_scale", ctypes.c_double), ("hess_scale", ctypes.c_double)]
 
 
+class Profile(ctypes.Structure):
+    _fields_ = [("hist_ms", ctypes.c_double), ("find_ms", ctypes.c_double), ("partition_ms", ctypes.c_double),
+                ("other_ms", ctypes.c_double), ("collective_ms", ctypes.c_double), ("hist_launches", ctypes.c_int64),
+                ("hist_rows", ctypes.c_int64), ("trees", ctypes.c_int64)]
+
+
 class ObjectiveConfig(ctypes.Structure):
     _fields_ = [("kind", ctypes.c_int32), ("lambdarank_target", ctypes.c_int32),
                 ("lambdarank_truncation_level", ctypes.c_int32), ("lambdarank_norm", ctypes.c_int32),
@@ -70,7 +76,7 @@ EXPORTED_SYMBOLS = [
     "gbl_learner_add_prediction_to_score", "gbl_learner_add_prediction_to_score_dev",
     "gbl_learner_get_leaf_assignment", "gbl_learner_get_leaf_indices", "gbl_learner_get_histogram",
     "gbl_learner_get_discretized", "gbl_learner_histogram_words", "gbl_learner_construct_histogram",
-    "gbl_learner_stream",
+    "gbl_learner_stream", "gbl_learner_set_profiling", "gbl_learner_get_profile",
     "gbl_objective_create", "gbl_objective_free", "gbl_objective_get_gradients", "gbl_objective_boost_from_score",
     "gbl_objective_is_constant_hessian",
     "gbl_device_malloc", "gbl_device_free", "gbl_memcpy_h2d", "gbl_memcpy_d2h", "gbl_device_fill_f64",
@@ -389,6 +395,14 @@ class Learner:
 
     def stream(self):
         return lib().gbl_learner_stream(self.handle)
+
+    def set_profiling(self, on):
+        check(lib().gbl_learner_set_profiling(self.handle, ctypes.c_int32(1 if on else 0)))
+
+    def profile(self, reset=False):
+        p = Profile()
+        check(lib().gbl_learner_get_profile(self.handle, ctypes.byref(p), ctypes.c_int32(1 if reset else 0)))
+        return {name: getattr(p, name) for name, _ in Profile._fields_}
 
     def free(self):
         if self.handle:

@@ -141,6 +141,8 @@ struct TreeState {
   double q_grad_scale, q_hess_scale, q_inv_grad_scale, q_inv_hess_scale;
   float max_abs_g, max_abs_h;
   double root_output;
+  long long hist_rows_total;  // sum of rows over this tree's histogram launches (algorithmic-bytes accounting)
+  long long hist_launches;
 };
 
 struct LearnerParams {  // by-value kernel argument

@@ -69,8 +69,14 @@ __device__ inline HistJob resolve_job(const LearnerDev& d, const int* explicit_i
   return j;
 }
 
+// Rows per chunk: one chunk per CTA when it fits under the flush cap, otherwise k equal rounds of chunks so that
+// every CTA gets the same number of chunks (no tail wave).
 __device__ inline int chunk_rows(int n, int grid_x, int cap) {
   int c = (n + grid_x - 1) / grid_x;
+  if (c > cap) {
+    const int k = (c + cap - 1) / cap;
+    c = (n + grid_x * k - 1) / (grid_x * k);
+  }
   c = max(c, kMinChunk);
   c = (c + 255) & ~255;
   return min(c, cap);

@@ -59,6 +59,47 @@ struct Learner {
   int graph_bag_count = -1;
   bool tree_pending = false;
   bool has_tree = false;
+  // profiling (CUDA events around every stage)
+  bool profiling = false;
+  std::vector<cudaEvent_t> ev;     // 2 per timed stage instance
+  std::vector<int> ev_stage;       // stage id per event pair
+  size_t ev_used = 0;
+  gbl_profile prof{};
+};
+
+enum Stage { kStageHist = 0, kStageFind = 1, kStagePart = 2, kStageOther = 3, kStageComm = 4 };
+
+struct StageTimer {
+  Learner* L;
+  cudaStream_t s;
+  size_t slot = 0;
+  bool on;
+  StageTimer(Learner* L_, cudaStream_t s_, int stage) : L(L_), s(s_), on(L_->profiling) {
+    if (!on) return;
+    if (L->ev_used + 2 > L->ev.size()) {
+      for (int k = 0; k < 2; ++k) {
+        cudaEvent_t e;
+        GBL_CUDA(cudaEventCreate(&e));
+        L->ev.push_back(e);
+      }
+      L->ev_stage.push_back(stage);
+    } else {
+      L->ev_stage[L->ev_used / 2] = stage;
+    }
+    slot = L->ev_used;
+    L->ev_used += 2;
+    record(L->ev[slot]);
+  }
+  ~StageTimer() {
+    if (on) record(L->ev[slot + 1]);
+  }
+  // Inside a stream capture the record must be an *external* event node, otherwise the event belongs to the
+  // capture and cannot be queried after the graph has run.
+  void record(cudaEvent_t e) {
+    cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+    cudaStreamIsCapturing(s, &st);
+    cudaEventRecordWithFlags(e, s, st == cudaStreamCaptureStatusActive ? cudaEventRecordExternal : cudaEventRecordDefault);
+  }
 };
 
 static void validate_config(const gbl_learner_config& c) {
@@ -210,6 +251,7 @@ static void learner_free(Learner* L) {
   cudaFree(L->hess_stage);
   cudaFree(L->tap_hist);
   if (L->ts_pinned) cudaFreeHost(L->ts_pinned);
+  for (cudaEvent_t e : L->ev) cudaEventDestroy(e);
   cudaStreamDestroy(L->stream);
   delete L;
 }
@@ -218,27 +260,45 @@ static void learner_free(Learner* L) {
 static void enqueue_tree(Learner* L, cudaStream_t s) {
   const LearnerDev& d = L->dev;
   const bool multi = L->comm != nullptr && L->comm->num_ranks > 1;
-  GBL_CUDA(cudaMemsetAsync(L->hist_pool, 0, sizeof(long long) * L->hist_pool_words, s));
-  launch_tree_begin(d, L->bag_indices, L->bag_count, s);
-  launch_maxabs(d, s);
+  L->ev_used = 0;
+  {
+    StageTimer tm(L, s, kStageOther);
+    GBL_CUDA(cudaMemsetAsync(L->hist_pool, 0, sizeof(long long) * L->hist_pool_words, s));
+    launch_tree_begin(d, L->bag_indices, L->bag_count, s);
+    launch_maxabs(d, s);
+  }
   if (multi) {
     // GradientDiscretizer: Network::GlobalSyncUpByMax (gradient_discretizer.cpp:101-104); also used for the
     // fixed-point scale in float mode so that every rank shares one scale.
+    StageTimer tm(L, s, kStageComm);
     comm_allreduce_f32(L->comm, &L->ts->max_abs_g, 2, RedOp::kMax, s);
   }
-  launch_scales_and_convert(d, s);
+  {
+    StageTimer tm(L, s, kStageOther);
+    launch_scales_and_convert(d, s);
+  }
   const int rounds = L->cfg.num_leaves - 1;
   for (int round = 0; round < rounds; ++round) {
-    launch_histogram(d, round, nullptr, -1, nullptr, s);
+    {
+      StageTimer tm(L, s, kStageHist);
+      launch_histogram(d, round, nullptr, -1, nullptr, s);
+    }
     if (multi) {
       // histogram + (smaller, larger) row counts in one all-reduce; replaces Network::ReduceScatter of
       // data_parallel_tree_learner.cpp:285-297 and the count sync of :457-458
+      StageTimer tm(L, s, kStageComm);
       comm_allreduce_i64(L->comm, L->hist_pool + static_cast<long long>(round) * d.slot_stride,
                          static_cast<size_t>(d.slot_stride), RedOp::kSum, s);
     }
-    if (round == 0) launch_root_init(d, s);
-    launch_find_best(d, round, s);
-    launch_partition(d, round, s);
+    {
+      StageTimer tm(L, s, kStageFind);
+      if (round == 0) launch_root_init(d, s);
+      launch_find_best(d, round, s);
+    }
+    {
+      StageTimer tm(L, s, kStagePart);
+      launch_partition(d, round, s);
+    }
   }
   GBL_CUDA(cudaMemcpyAsync(L->records_pinned, L->records, sizeof(gbl_split_record) * rounds, cudaMemcpyDeviceToHost, s));
   GBL_CUDA(cudaMemcpyAsync(L->ts_pinned, L->ts, sizeof(TreeState), cudaMemcpyDeviceToHost, s));
@@ -298,6 +358,22 @@ static void train_finish(Learner* L, gbl_tree_result* result, gbl_split_record* 
   const TreeState& t = *L->ts_pinned;
   const int ns = t.num_splits;
   if (ns < 0 || ns > L->cfg.num_leaves - 1) fatal("learner: corrupt tree state (num_splits=%d)", ns);
+  if (L->profiling) {
+    for (size_t i = 0; i + 1 < L->ev_used; i += 2) {
+      float ms = 0.f;
+      GBL_CUDA(cudaEventElapsedTime(&ms, L->ev[i], L->ev[i + 1]));
+      switch (L->ev_stage[i / 2]) {
+        case kStageHist: L->prof.hist_ms += ms; break;
+        case kStageFind: L->prof.find_ms += ms; break;
+        case kStagePart: L->prof.partition_ms += ms; break;
+        case kStageComm: L->prof.collective_ms += ms; break;
+        default: L->prof.other_ms += ms; break;
+      }
+    }
+    L->prof.trees += 1;
+  }
+  L->prof.hist_launches += t.hist_launches;  // counted on the device whether or not stages are timed
+  L->prof.hist_rows += t.hist_rows_total;
   const bool multi = L->comm != nullptr && L->comm->num_ranks > 1;
   if (multi && ns > 0) {
     // global leaf counts of every split (data_parallel_tree_learner.cpp:457-458): one all-reduce per tree
@@ -607,6 +683,26 @@ int gbl_learner_construct_histogram(gbl_learner* learner, const int32_t* indices
   DeviceGuard guard(L->ds->device);
   launch_histogram(L->dev, 0, indices_dev, static_cast<int>(num_indices), reinterpret_cast<long long*>(out_hist_dev),
                    L->stream);
+  GBL_API_END();
+}
+
+int gbl_learner_set_profiling(gbl_learner* learner, int32_t enabled) {
+  GBL_API_BEGIN();
+  Learner* L = LEARNER(learner);
+  if (L == nullptr) fatal("gbl_learner_set_profiling: null learner");
+  DeviceGuard guard(L->ds->device);
+  GBL_CUDA(cudaStreamSynchronize(L->stream));
+  drop_graph(L);
+  L->profiling = enabled != 0;
+  GBL_API_END();
+}
+
+int gbl_learner_get_profile(gbl_learner* learner, gbl_profile* out, int32_t reset) {
+  GBL_API_BEGIN();
+  Learner* L = LEARNER(learner);
+  if (L == nullptr || out == nullptr) fatal("gbl_learner_get_profile: null argument");
+  *out = L->prof;
+  if (reset) L->prof = gbl_profile{};
   GBL_API_END();
 }
 

@@ -234,6 +234,10 @@ __global__ void __launch_bounds__(kPartThreads) part_scatter_kernel(LearnerDev d
       if (nl < d.p.min_data_in_leaf * 2 && nr < d.p.min_data_in_leaf * 2) skip = 1;
     }
     t.skip_hist = skip;
+    if (!skip && r + 1 < d.p.num_leaves) {
+      t.hist_rows_total += ns;
+      t.hist_launches += 1;
+    }
     t.split_left_total = nl;
     t.num_leaves_cur = r + 1;
     t.num_splits += 1;

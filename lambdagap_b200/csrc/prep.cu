@@ -58,6 +58,8 @@ __global__ void __launch_bounds__(256) tree_begin_kernel(LearnerDev d, int root_
     t.max_abs_g = 0.f;
     t.max_abs_h = 0.f;
     t.root_output = 0.0;
+    t.hist_rows_total = root_count;
+    t.hist_launches = 1;
     d.leaves[0].count = root_count;
     d.leaves[0].global_count = root_count;
     // data-parallel: the local root count rides in the tail of slot 0 through the histogram all-reduce

@@ -29,6 +29,9 @@ lrn = capi.Learner(ds, cfg)
 score = np.zeros(n)
 gbuf = capi.DeviceBuffer(4 * n)
 hbuf = capi.DeviceBuffer(4 * n)
+import os
+if os.environ.get('GBL_PROF'):
+    lrn.set_profiling(True)
 for t in range(trees):
     p = 1 / (1 + np.exp(-score))
     g = (p - y).astype(np.float32)
@@ -41,6 +44,8 @@ for t in range(trees):
     res, recs = lrn.train(gbuf, hbuf)
     dt = time.time() - t0
     print("tree %d: %.2f ms, splits=%d launches=%d" % (t, dt * 1e3, res["num_splits"], capi.kernel_launch_count() - l0), flush=True)
+    if os.environ.get('GBL_PROF'):
+        print("profile", lrn.profile(reset=True), flush=True)
     sizes = [n] + [min(r["left_count"], r["right_count"]) for r in recs]
     print("hist_rows", " ".join(str(x) for x in sizes[:len(recs)]), flush=True)
     assign = lrn.leaf_assignment()
