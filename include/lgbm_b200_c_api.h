@@ -1,0 +1,80 @@
+/*
+ * lgbm_b200_c_api.h -- the subset of the reference's C API (include/LightGBM/c_api.h) that the B200 host
+ * library (lambdagap_b200/lib/liblgbm_b200.so) exports under the SAME names and signatures, so that a program
+ * written against lib_lightgbm.so for the histogram-GBDT hot path (dense matrices; objectives regression /
+ * binary / lambdarank incl. the fork's 18 lambdarank_target values; device_type=cuda) can switch libraries.
+ * Each entry cites the reference definition it replaces.  Return 0 on success, -1 on error
+ * (LGBM_GetLastError), exactly like API_BEGIN/API_END (src/c_api.cpp:38-52).
+ */
+#ifndef LGBM_B200_C_API_H_
+#define LGBM_B200_C_API_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* DatasetHandle; /* include/LightGBM/c_api.h:27 */
+typedef void* BoosterHandle; /* :28 */
+
+#define C_API_DTYPE_FLOAT32 (0) /* :30 */
+#define C_API_DTYPE_FLOAT64 (1)
+#define C_API_DTYPE_INT32 (2)
+#define C_API_PREDICT_NORMAL (0)    /* :35 */
+#define C_API_PREDICT_RAW_SCORE (1) /* :36 */
+
+#define LGBM_B200_EXPORT __attribute__((visibility("default")))
+
+/* src/c_api.cpp:54 */
+LGBM_B200_EXPORT const char* LGBM_GetLastError(void);
+/* src/c_api.cpp:1303 (c_api.h:409) */
+LGBM_B200_EXPORT int LGBM_DatasetCreateFromMat(const void* data, int data_type, int32_t nrow, int32_t ncol,
+                                               int is_row_major, const char* parameters,
+                                               const DatasetHandle reference, DatasetHandle* out);
+/* src/c_api.cpp:1760 (c_api.h:552) */
+LGBM_B200_EXPORT int LGBM_DatasetSetField(DatasetHandle handle, const char* field_name, const void* field_data,
+                                          int num_element, int type);
+/* src/c_api.cpp:1850,1858 */
+LGBM_B200_EXPORT int LGBM_DatasetGetNumData(DatasetHandle handle, int32_t* out);
+LGBM_B200_EXPORT int LGBM_DatasetGetNumFeature(DatasetHandle handle, int32_t* out);
+/* src/c_api.cpp:1711 */
+LGBM_B200_EXPORT int LGBM_DatasetFree(DatasetHandle handle);
+/* src/c_api.cpp:1953 (c_api.h:656) */
+LGBM_B200_EXPORT int LGBM_BoosterCreate(const DatasetHandle train_data, const char* parameters, BoosterHandle* out);
+/* src/c_api.cpp:1994 */
+LGBM_B200_EXPORT int LGBM_BoosterFree(BoosterHandle handle);
+/* src/c_api.cpp:2076 (c_api.h:769) */
+LGBM_B200_EXPORT int LGBM_BoosterUpdateOneIter(BoosterHandle handle, int* is_finished);
+/* src/c_api.cpp:2087 (c_api.h:801) */
+LGBM_B200_EXPORT int LGBM_BoosterUpdateOneIterCustom(BoosterHandle handle, const float* grad, const float* hess,
+                                                     int* is_finished);
+/* src/c_api.cpp:2112,2119 */
+LGBM_B200_EXPORT int LGBM_BoosterGetCurrentIteration(BoosterHandle handle, int* out_iteration);
+LGBM_B200_EXPORT int LGBM_BoosterNumberOfTotalModel(BoosterHandle handle, int* out_models);
+/* src/c_api.cpp:2200,2209 */
+LGBM_B200_EXPORT int LGBM_BoosterGetNumPredict(BoosterHandle handle, int data_idx, int64_t* out_len);
+LGBM_B200_EXPORT int LGBM_BoosterGetPredict(BoosterHandle handle, int data_idx, int64_t* out_len, double* out_result);
+/* src/c_api.cpp:2483 */
+LGBM_B200_EXPORT int LGBM_BoosterPredictForMat(BoosterHandle handle, const void* data, int data_type, int32_t nrow,
+                                               int32_t ncol, int is_row_major, int predict_type, int start_iteration,
+                                               int num_iteration, const char* parameter, int64_t* out_len,
+                                               double* out_result);
+/* src/c_api.cpp:2640 */
+LGBM_B200_EXPORT int LGBM_BoosterSaveModelToString(BoosterHandle handle, int start_iteration, int num_iteration,
+                                                   int feature_importance_type, int64_t buffer_len, int64_t* out_len,
+                                                   char* out_str);
+/* NCCL counterpart of LGBM_NetworkInitWithFunctions (src/c_api.cpp:2787-2795): binds this host thread / process
+ * as rank `rank` of `num_machines` using a 128-byte NCCL unique id distributed by the caller
+ * (LGBM_NetworkGetNcclUniqueId on rank 0).  Boosters created afterwards with tree_learner=data shard rows. */
+LGBM_B200_EXPORT int LGBM_NetworkGetNcclUniqueId(uint8_t out_id[128]);
+LGBM_B200_EXPORT int LGBM_NetworkInitWithNccl(const uint8_t id[128], int num_machines, int rank, int device_id);
+/* src/c_api.cpp:2781 */
+LGBM_B200_EXPORT int LGBM_NetworkFree(void);
+/* not in the reference: raw (unconverted) training scores, device -> host */
+LGBM_B200_EXPORT int LGBM_BoosterGetTrainScoreRaw(BoosterHandle handle, int64_t* out_len, double* out_result);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LGBM_B200_C_API_H_ */

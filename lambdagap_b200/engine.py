@@ -1,0 +1,167 @@
+"""Python front of the host library (lambdagap_b200/lib/liblgbm_b200.so): the reference's C API names
+(include/lgbm_b200_c_api.h <-> include/LightGBM/c_api.h) through ctypes, the way the reference's own
+python-package/lightgbm/basic.py binds lib_lightgbm.so.  No compute here; no CPU fallback anywhere below.
+"""
+import ctypes
+import os
+
+import numpy as np
+
+from . import capi
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+HOST_LIB_PATH = os.path.join(_HERE, "lib", "liblgbm_b200.so")
+C_API_DTYPE_FLOAT32, C_API_DTYPE_FLOAT64, C_API_DTYPE_INT32 = 0, 1, 2
+
+LGBM_EXPORTED_SYMBOLS = [
+    "LGBM_GetLastError", "LGBM_DatasetCreateFromMat", "LGBM_DatasetSetField", "LGBM_DatasetGetNumData",
+    "LGBM_DatasetGetNumFeature", "LGBM_DatasetFree", "LGBM_BoosterCreate", "LGBM_BoosterFree",
+    "LGBM_BoosterUpdateOneIter", "LGBM_BoosterUpdateOneIterCustom", "LGBM_BoosterGetCurrentIteration",
+    "LGBM_BoosterNumberOfTotalModel", "LGBM_BoosterGetNumPredict", "LGBM_BoosterGetPredict",
+    "LGBM_BoosterPredictForMat", "LGBM_BoosterSaveModelToString", "LGBM_NetworkGetNcclUniqueId",
+    "LGBM_NetworkInitWithNccl", "LGBM_NetworkFree", "LGBM_BoosterGetTrainScoreRaw",
+]
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        capi.lib()  # the CUDA library first: fails loudly when it is missing
+        if not os.path.exists(HOST_LIB_PATH):
+            raise capi.GblError("%s not found: run __graft_entry__.build() (make -C lambdagap_b200/host)" % HOST_LIB_PATH)
+        _lib = ctypes.CDLL(HOST_LIB_PATH)
+        _lib.LGBM_GetLastError.restype = ctypes.c_char_p
+    return _lib
+
+
+class LightGBMError(RuntimeError):
+    pass
+
+
+def _check(ret):
+    if ret != 0:
+        raise LightGBMError(lib().LGBM_GetLastError().decode())
+
+
+def _params(p):
+    if p is None:
+        return b""
+    if isinstance(p, bytes):
+        return p
+    if isinstance(p, str):
+        return p.encode()
+    return " ".join("%s=%s" % (k, v) for k, v in p.items()).encode()
+
+
+class Dataset:
+    def __init__(self, X, label=None, group=None, weight=None, params=None, reference=None):
+        X = np.ascontiguousarray(X)
+        if X.dtype not in (np.float32, np.float64):
+            X = X.astype(np.float32)
+        self.n, self.f = X.shape
+        self.handle = ctypes.c_void_p()
+        dt = C_API_DTYPE_FLOAT32 if X.dtype == np.float32 else C_API_DTYPE_FLOAT64
+        _check(lib().LGBM_DatasetCreateFromMat(
+            X.ctypes.data_as(ctypes.c_void_p), ctypes.c_int(dt), ctypes.c_int32(self.n), ctypes.c_int32(self.f),
+            ctypes.c_int(1), ctypes.c_char_p(_params(params)), reference.handle if reference is not None else None,
+            ctypes.byref(self.handle)))
+        if label is not None:
+            self.set_field("label", np.asarray(label, dtype=np.float32))
+        if weight is not None:
+            self.set_field("weight", np.asarray(weight, dtype=np.float32))
+        if group is not None:
+            self.set_field("group", np.asarray(group, dtype=np.int32))
+
+    def set_field(self, name, arr):
+        arr = np.ascontiguousarray(arr)
+        dt = {np.dtype(np.float32): C_API_DTYPE_FLOAT32, np.dtype(np.float64): C_API_DTYPE_FLOAT64,
+              np.dtype(np.int32): C_API_DTYPE_INT32}[arr.dtype]
+        _check(lib().LGBM_DatasetSetField(self.handle, ctypes.c_char_p(name.encode()),
+                                          arr.ctypes.data_as(ctypes.c_void_p), ctypes.c_int(len(arr)), ctypes.c_int(dt)))
+
+    def free(self):
+        if self.handle:
+            lib().LGBM_DatasetFree(self.handle)
+            self.handle = None
+
+
+class Booster:
+    def __init__(self, train_set, params):
+        self.train_set = train_set
+        self.handle = ctypes.c_void_p()
+        _check(lib().LGBM_BoosterCreate(train_set.handle, ctypes.c_char_p(_params(params)), ctypes.byref(self.handle)))
+
+    def update(self):
+        fin = ctypes.c_int(0)
+        _check(lib().LGBM_BoosterUpdateOneIter(self.handle, ctypes.byref(fin)))
+        return fin.value
+
+    def update_custom(self, grad, hess):
+        fin = ctypes.c_int(0)
+        grad = np.ascontiguousarray(grad, dtype=np.float32)
+        hess = np.ascontiguousarray(hess, dtype=np.float32)
+        _check(lib().LGBM_BoosterUpdateOneIterCustom(self.handle, grad.ctypes.data_as(ctypes.c_void_p),
+                                                     hess.ctypes.data_as(ctypes.c_void_p), ctypes.byref(fin)))
+        return fin.value
+
+    def current_iteration(self):
+        out = ctypes.c_int(0)
+        _check(lib().LGBM_BoosterGetCurrentIteration(self.handle, ctypes.byref(out)))
+        return out.value
+
+    def train_scores(self, raw=True):
+        n = ctypes.c_int64(0)
+        _check(lib().LGBM_BoosterGetNumPredict(self.handle, ctypes.c_int(0), ctypes.byref(n)))
+        out = np.zeros(n.value, dtype=np.float64)
+        if raw:
+            _check(lib().LGBM_BoosterGetTrainScoreRaw(self.handle, ctypes.byref(n), out.ctypes.data_as(ctypes.c_void_p)))
+        else:
+            _check(lib().LGBM_BoosterGetPredict(self.handle, ctypes.c_int(0), ctypes.byref(n),
+                                                out.ctypes.data_as(ctypes.c_void_p)))
+        return out
+
+    def predict(self, X, raw_score=False):
+        X = np.ascontiguousarray(X)
+        if X.dtype not in (np.float32, np.float64):
+            X = X.astype(np.float64)
+        dt = C_API_DTYPE_FLOAT32 if X.dtype == np.float32 else C_API_DTYPE_FLOAT64
+        out = np.zeros(X.shape[0], dtype=np.float64)
+        n = ctypes.c_int64(0)
+        _check(lib().LGBM_BoosterPredictForMat(self.handle, X.ctypes.data_as(ctypes.c_void_p), ctypes.c_int(dt),
+                                               ctypes.c_int32(X.shape[0]), ctypes.c_int32(X.shape[1]), ctypes.c_int(1),
+                                               ctypes.c_int(1 if raw_score else 0), ctypes.c_int(0), ctypes.c_int(-1),
+                                               ctypes.c_char_p(b""), ctypes.byref(n), out.ctypes.data_as(ctypes.c_void_p)))
+        return out
+
+    def model_to_string(self):
+        need = ctypes.c_int64(0)
+        buf = ctypes.create_string_buffer(1 << 20)
+        _check(lib().LGBM_BoosterSaveModelToString(self.handle, ctypes.c_int(0), ctypes.c_int(-1), ctypes.c_int(0),
+                                                   ctypes.c_int64(len(buf)), ctypes.byref(need), buf))
+        if need.value > len(buf):
+            buf = ctypes.create_string_buffer(need.value)
+            _check(lib().LGBM_BoosterSaveModelToString(self.handle, ctypes.c_int(0), ctypes.c_int(-1), ctypes.c_int(0),
+                                                       ctypes.c_int64(len(buf)), ctypes.byref(need), buf))
+        return buf.value.decode()
+
+    def free(self):
+        if self.handle:
+            lib().LGBM_BoosterFree(self.handle)
+            self.handle = None
+
+
+def network_init_nccl(unique_id, num_machines, rank, device_id):
+    buf = (ctypes.c_uint8 * 128).from_buffer_copy(bytes(unique_id))
+    _check(lib().LGBM_NetworkInitWithNccl(buf, ctypes.c_int(num_machines), ctypes.c_int(rank), ctypes.c_int(device_id)))
+
+
+def network_unique_id():
+    buf = (ctypes.c_uint8 * 128)()
+    _check(lib().LGBM_NetworkGetNcclUniqueId(buf))
+    return bytes(buf)
+
+
+def network_free():
+    _check(lib().LGBM_NetworkFree())

@@ -1,0 +1,201 @@
+// c_api.cpp -- the reference's C API names for the hot-path subset (see include/lgbm_b200_c_api.h).
+// Reference: src/c_api.cpp (Booster class :169-195, :410-423; API_BEGIN/API_END :38-52).
+#include <cstring>
+#include <mutex>
+
+#include "lgbm_b200_c_api.h"
+#include "lgbm_host.h"
+
+using namespace lgbm_b200;
+
+namespace {
+
+thread_local char g_last_error[1024] = "Everything is fine";
+thread_local gbl_comm* g_comm = nullptr;  // Network state is thread_local in the reference (src/network/network.cpp:17-27)
+thread_local int g_num_machines = 1;
+
+void SetLastError(const char* msg) {
+  std::strncpy(g_last_error, msg, sizeof(g_last_error) - 1);
+  g_last_error[sizeof(g_last_error) - 1] = '\0';
+}
+
+#define API_BEGIN() try {
+#define API_END()                                                  \
+  }                                                                \
+  catch (std::exception & ex) { SetLastError(ex.what()); return -1; } \
+  catch (...) { SetLastError("unknown exception"); return -1; }    \
+  return 0;
+
+// Booster (src/c_api.cpp:143-900): owns config, objective and boosting; one writer at a time
+struct Booster {
+  Config config;
+  std::unique_ptr<ObjectiveFunction> objective;
+  std::unique_ptr<GBDT> boosting;
+  std::mutex mutex;
+  Booster(const Dataset* train_data, const char* parameters) {
+    config.Set(parameters ? parameters : "");
+    // Booster ctor :185-191: a parallel learner without machines falls back to serial
+    if (g_num_machines <= 1 && config.tree_learner != "serial") {
+      Log::Warning("Only find one worker, will switch to serial tree learner");
+      config.tree_learner = "serial";
+    }
+    if (g_num_machines > 1 && config.tree_learner == "serial") config.tree_learner = "data";
+    objective.reset(ObjectiveFunction::CreateObjectiveFunction(config.objective, config));
+    boosting.reset(new GBDT());
+    boosting->Init(&config, train_data, objective.get(), g_num_machines > 1 ? g_comm : nullptr);
+  }
+};
+
+}  // namespace
+
+extern "C" {
+
+const char* LGBM_GetLastError(void) { return g_last_error; }
+
+int LGBM_DatasetCreateFromMat(const void* data, int data_type, int32_t nrow, int32_t ncol, int is_row_major,
+                              const char* parameters, const DatasetHandle reference, DatasetHandle* out) {
+  API_BEGIN();
+  Config config;
+  config.Set(parameters ? parameters : "");
+  *out = Dataset::CreateFromMat(data, data_type, nrow, ncol, is_row_major, config,
+                                reinterpret_cast<const Dataset*>(reference));
+  API_END();
+}
+
+int LGBM_DatasetSetField(DatasetHandle handle, const char* field_name, const void* field_data, int num_element,
+                         int type) {
+  API_BEGIN();
+  reinterpret_cast<Dataset*>(handle)->SetField(field_name, field_data, num_element, type);
+  API_END();
+}
+
+int LGBM_DatasetGetNumData(DatasetHandle handle, int32_t* out) {
+  API_BEGIN();
+  *out = reinterpret_cast<Dataset*>(handle)->num_data();
+  API_END();
+}
+
+int LGBM_DatasetGetNumFeature(DatasetHandle handle, int32_t* out) {
+  API_BEGIN();
+  *out = reinterpret_cast<Dataset*>(handle)->num_total_features();
+  API_END();
+}
+
+int LGBM_DatasetFree(DatasetHandle handle) {
+  API_BEGIN();
+  delete reinterpret_cast<Dataset*>(handle);
+  API_END();
+}
+
+int LGBM_BoosterCreate(const DatasetHandle train_data, const char* parameters, BoosterHandle* out) {
+  API_BEGIN();
+  *out = new Booster(reinterpret_cast<const Dataset*>(train_data), parameters);
+  API_END();
+}
+
+int LGBM_BoosterFree(BoosterHandle handle) {
+  API_BEGIN();
+  delete reinterpret_cast<Booster*>(handle);
+  API_END();
+}
+
+int LGBM_BoosterUpdateOneIter(BoosterHandle handle, int* is_finished) {
+  API_BEGIN();
+  Booster* b = reinterpret_cast<Booster*>(handle);
+  std::lock_guard<std::mutex> lock(b->mutex);
+  *is_finished = b->boosting->TrainOneIter(nullptr, nullptr) ? 1 : 0;
+  API_END();
+}
+
+int LGBM_BoosterUpdateOneIterCustom(BoosterHandle handle, const float* grad, const float* hess, int* is_finished) {
+  API_BEGIN();
+  Booster* b = reinterpret_cast<Booster*>(handle);
+  std::lock_guard<std::mutex> lock(b->mutex);
+  *is_finished = b->boosting->TrainOneIter(grad, hess) ? 1 : 0;
+  API_END();
+}
+
+int LGBM_BoosterGetCurrentIteration(BoosterHandle handle, int* out_iteration) {
+  API_BEGIN();
+  *out_iteration = reinterpret_cast<Booster*>(handle)->boosting->GetCurrentIteration();
+  API_END();
+}
+
+int LGBM_BoosterNumberOfTotalModel(BoosterHandle handle, int* out_models) {
+  API_BEGIN();
+  *out_models = reinterpret_cast<Booster*>(handle)->boosting->NumberOfTotalModel();
+  API_END();
+}
+
+int LGBM_BoosterGetNumPredict(BoosterHandle handle, int data_idx, int64_t* out_len) {
+  API_BEGIN();
+  *out_len = reinterpret_cast<Booster*>(handle)->boosting->GetNumPredictAt(data_idx);
+  API_END();
+}
+
+int LGBM_BoosterGetPredict(BoosterHandle handle, int data_idx, int64_t* out_len, double* out_result) {
+  API_BEGIN();
+  Booster* b = reinterpret_cast<Booster*>(handle);
+  std::lock_guard<std::mutex> lock(b->mutex);
+  b->boosting->GetPredictAt(data_idx, out_result, out_len);
+  API_END();
+}
+
+int LGBM_BoosterGetTrainScoreRaw(BoosterHandle handle, int64_t* out_len, double* out_result) {
+  API_BEGIN();
+  Booster* b = reinterpret_cast<Booster*>(handle);
+  std::lock_guard<std::mutex> lock(b->mutex);
+  b->boosting->GetTrainScore(out_result);
+  *out_len = b->boosting->GetNumPredictAt(0);
+  API_END();
+}
+
+int LGBM_BoosterPredictForMat(BoosterHandle handle, const void* data, int data_type, int32_t nrow, int32_t ncol,
+                              int is_row_major, int predict_type, int start_iteration, int num_iteration,
+                              const char* /*parameter*/, int64_t* out_len, double* out_result) {
+  API_BEGIN();
+  Booster* b = reinterpret_cast<Booster*>(handle);
+  if (predict_type != C_API_PREDICT_NORMAL && predict_type != C_API_PREDICT_RAW_SCORE)
+    Log::Fatal("predict_type %d is not supported by the B200 host layer (normal, raw score)", predict_type);
+  if (start_iteration > 0 || (num_iteration > 0 && num_iteration < b->boosting->NumberOfTotalModel()))
+    Log::Fatal("partial-model prediction is not supported by the B200 host layer");
+  b->boosting->PredictForMat(data, data_type, nrow, ncol, is_row_major, predict_type == C_API_PREDICT_RAW_SCORE, out_result);
+  *out_len = nrow;
+  API_END();
+}
+
+int LGBM_BoosterSaveModelToString(BoosterHandle handle, int start_iteration, int num_iteration,
+                                  int /*feature_importance_type*/, int64_t buffer_len, int64_t* out_len, char* out_str) {
+  API_BEGIN();
+  Booster* b = reinterpret_cast<Booster*>(handle);
+  const std::string model = b->boosting->SaveModelToString(start_iteration, num_iteration);
+  *out_len = static_cast<int64_t>(model.size()) + 1;
+  if (*out_len <= buffer_len) std::memcpy(out_str, model.c_str(), *out_len);
+  API_END();
+}
+
+int LGBM_NetworkGetNcclUniqueId(uint8_t out_id[128]) {
+  API_BEGIN();
+  GblCheck(gbl_comm_get_unique_id(out_id));
+  API_END();
+}
+
+int LGBM_NetworkInitWithNccl(const uint8_t id[128], int num_machines, int rank, int device_id) {
+  API_BEGIN();
+  if (g_comm != nullptr) Log::Fatal("Network already initialised on this thread");
+  if (num_machines > 1) {
+    GblCheck(gbl_comm_create(id, num_machines, rank, device_id, &g_comm));
+    g_num_machines = num_machines;
+  }
+  API_END();
+}
+
+int LGBM_NetworkFree(void) {
+  API_BEGIN();
+  if (g_comm != nullptr) gbl_comm_free(g_comm);
+  g_comm = nullptr;
+  g_num_machines = 1;
+  API_END();
+}
+
+}  // extern "C"

@@ -1,0 +1,203 @@
+// gbdt.cpp -- the boosting loop above the tree learner, device-resident (scores, gradients and hessians never
+// leave HBM; per iteration only the split records of the new tree come back).
+//
+// Reference: GBDT::Init (src/boosting/gbdt.cpp:53-162), BoostFromAverage (:319-343), Boosting (:222-237),
+// TrainOneIter (:346-454), UpdateScore (:495-524), GetPredictAt (:686-720), SaveModelToString
+// (src/boosting/gbdt_model_text.cpp:311-400), ScoreUpdater (src/boosting/score_updater.hpp:22-125; the device
+// variant src/boosting/cuda/cuda_score_updater.cpp:12-80).
+#include <algorithm>
+#include <cstring>
+#include <sstream>
+
+#include "lgbm_host.h"
+
+namespace lgbm_b200 {
+
+GBDT::~GBDT() {
+  if (score_dev_) gbl_device_free(device_id_, score_dev_);
+  if (grad_dev_) gbl_device_free(device_id_, grad_dev_);
+  if (hess_dev_) gbl_device_free(device_id_, hess_dev_);
+}
+
+void GBDT::Init(const Config* config, const Dataset* train_data, ObjectiveFunction* objective, gbl_comm* comm) {
+  if (train_data == nullptr) Log::Fatal("GBDT::Init: no training data");
+  config_ = config;
+  train_data_ = train_data;
+  objective_function_ = objective;
+  num_data_ = train_data->num_data();
+  shrinkage_rate_ = config->learning_rate;
+  device_id_ = train_data->device_id();
+  max_feature_idx_ = train_data->num_total_features() - 1;
+  iter_ = 0;
+  bool is_constant_hessian = false;
+  if (objective_function_ != nullptr) {
+    objective_function_->Init(train_data->metadata(), num_data_, device_id_);
+    is_constant_hessian = objective_function_->IsConstantHessian();
+  }
+  tree_learner_.reset(TreeLearner::CreateTreeLearner(comm != nullptr ? "data" : config->tree_learner == "serial" ? "serial" : config->tree_learner,
+                                                     config->device_type, config, comm));
+  tree_learner_->Init(train_data, is_constant_hessian);
+  void* p = nullptr;
+  GblCheck(gbl_device_malloc(device_id_, sizeof(double) * num_data_, &p));
+  score_dev_ = static_cast<double*>(p);
+  GblCheck(gbl_device_fill_f64(device_id_, score_dev_, 0.0, num_data_));
+  GblCheck(gbl_device_malloc(device_id_, sizeof(float) * num_data_, &p));
+  grad_dev_ = static_cast<float*>(p);
+  GblCheck(gbl_device_malloc(device_id_, sizeof(float) * num_data_, &p));
+  hess_dev_ = static_cast<float*>(p);
+}
+
+double GBDT::BoostFromAverage() {
+  // gbdt.cpp:319-343 (single GPU: no Network::GlobalSyncUpByMean)
+  if (models_.empty() && !has_init_score_ && objective_function_ != nullptr && config_->boost_from_average) {
+    const double init_score = objective_function_->BoostFromScore(0);
+    if (std::fabs(init_score) > kEpsilon) {
+      // ScoreUpdater::AddScore(val): one fill since all scores are still zero
+      GblCheck(gbl_device_fill_f64(device_id_, score_dev_, init_score, num_data_));
+      Log::Info("Start training from score %lf", init_score);
+      return init_score;
+    }
+  }
+  return 0.0;
+}
+
+bool GBDT::TrainOneIter(const score_t* gradients, const score_t* hessians) {
+  double init_score = 0.0;
+  if (gradients == nullptr || hessians == nullptr) {
+    if (objective_function_ == nullptr) Log::Fatal("No objective function provided");
+    init_score = BoostFromAverage();
+    // GBDT::Boosting, enqueued on the learner's stream so that no host synchronisation is needed before Train
+    B200TreeLearner* bl = dynamic_cast<B200TreeLearner*>(tree_learner_.get());
+    objective_function_->GetGradients(score_dev_, grad_dev_, hess_dev_, bl ? gbl_learner_stream(bl->handle()) : nullptr);
+    if (bl == nullptr) GblCheck(gbl_device_synchronize(device_id_));
+  } else {
+    if (objective_function_ != nullptr) Log::Fatal("Check failed: (objective_function_) == (nullptr): pass objective=custom to use custom gradients");
+    GblCheck(gbl_memcpy_h2d(device_id_, grad_dev_, gradients, sizeof(float) * num_data_));
+    GblCheck(gbl_memcpy_h2d(device_id_, hess_dev_, hessians, sizeof(float) * num_data_));
+  }
+  const bool is_first_tree = models_.empty();
+  std::unique_ptr<Tree> new_tree(tree_learner_->Train(grad_dev_, hess_dev_, is_first_tree));
+  bool should_continue = false;
+  if (new_tree->num_leaves() > 1) {
+    should_continue = true;
+    new_tree->Shrinkage(shrinkage_rate_);
+    tree_learner_->AddPredictionToScore(new_tree.get(), score_dev_);  // UpdateScore
+    if (std::fabs(init_score) > kEpsilon) new_tree->AddBias(init_score);
+  } else {
+    if (models_.empty()) {
+      if (objective_function_ != nullptr && !config_->boost_from_average && !has_init_score_) {
+        init_score = objective_function_->BoostFromScore(0);
+        GblCheck(gbl_device_fill_f64(device_id_, score_dev_, init_score, num_data_));
+      }
+      new_tree->AsConstantTree(init_score, num_data_);
+    } else {
+      new_tree->AsConstantTree(0, num_data_);
+    }
+  }
+  models_.push_back(std::move(new_tree));
+  if (!should_continue) {
+    Log::Warning("Stopped training because there are no more leaves that meet the split requirements");
+    if (models_.size() > 1) models_.pop_back();
+    return true;
+  }
+  ++iter_;
+  return false;
+}
+
+int64_t GBDT::GetNumPredictAt(int data_idx) const {
+  if (data_idx != 0) Log::Fatal("Only the training data (data_idx=0) is attached to this booster");
+  return num_data_;
+}
+
+void GBDT::GetTrainScore(double* out) const {
+  GblCheck(gbl_memcpy_d2h(device_id_, out, score_dev_, sizeof(double) * num_data_));
+}
+
+void GBDT::GetPredictAt(int data_idx, double* out_result, int64_t* out_len) {
+  if (data_idx != 0) Log::Fatal("Only the training data (data_idx=0) is attached to this booster");
+  GetTrainScore(out_result);
+  if (objective_function_ != nullptr) {
+    for (int i = 0; i < num_data_; ++i) {
+      double v;
+      objective_function_->ConvertOutput(out_result + i, &v);
+      out_result[i] = v;
+    }
+  }
+  *out_len = num_data_;
+}
+
+std::string GBDT::SaveModelToString(int start_iteration, int num_iteration) const {
+  std::stringstream ss;
+  ss << "tree" << '\n';
+  ss << "version=v4" << '\n';
+  ss << "num_class=1" << '\n';
+  ss << "num_tree_per_iteration=1" << '\n';
+  ss << "label_index=0" << '\n';
+  ss << "max_feature_idx=" << max_feature_idx_ << '\n';
+  if (objective_function_ != nullptr) ss << "objective=" << objective_function_->ToString() << '\n';
+  auto join = [](const std::vector<std::string>& v) {
+    std::string s;
+    for (size_t i = 0; i < v.size(); ++i) {
+      if (i) s.push_back(' ');
+      s += v[i];
+    }
+    return s;
+  };
+  ss << "feature_names=" << join(train_data_->feature_names()) << '\n';
+  ss << "feature_infos=" << join(train_data_->feature_infos()) << '\n';
+  int num_used = static_cast<int>(models_.size());
+  start_iteration = std::max(start_iteration, 0);
+  start_iteration = std::min(start_iteration, num_used);
+  if (num_iteration > 0) num_used = std::min(start_iteration + num_iteration, num_used);
+  std::vector<std::string> tree_strs;
+  std::string sizes;
+  for (int i = start_iteration; i < num_used; ++i) {
+    std::string t = "Tree=" + std::to_string(i - start_iteration) + '\n' + models_[i]->ToString() + '\n';
+    if (!sizes.empty()) sizes.push_back(' ');
+    sizes += std::to_string(t.size());
+    tree_strs.push_back(std::move(t));
+  }
+  ss << "tree_sizes=" << sizes << '\n' << '\n';
+  for (const auto& t : tree_strs) ss << t;
+  ss << "end of trees" << "\n";
+  // feature importances (split counts), gbdt_model_text.cpp:368-389
+  std::vector<size_t> imp(max_feature_idx_ + 1, 0);
+  for (int i = start_iteration; i < num_used; ++i) {
+    for (int n = 0; n < models_[i]->num_leaves() - 1; ++n) imp[models_[i]->split_feature(n)] += 1;
+  }
+  std::vector<std::pair<size_t, std::string>> pairs;
+  const auto names = train_data_->feature_names();
+  for (size_t i = 0; i < imp.size(); ++i) {
+    if (imp[i] > 0) pairs.emplace_back(imp[i], names[i]);
+  }
+  std::stable_sort(pairs.begin(), pairs.end(),
+                   [](const std::pair<size_t, std::string>& a, const std::pair<size_t, std::string>& b) { return a.first > b.first; });
+  ss << '\n' << "feature_importances:" << '\n';
+  for (const auto& p : pairs) ss << p.second << "=" << p.first << '\n';
+  ss << "\nparameters:" << '\n' << config_->ToString() << "\n" << "end of parameters" << '\n';
+  return ss.str();
+}
+
+void GBDT::PredictForMat(const void* data, int data_type, int32_t nrow, int32_t ncol, int is_row_major, bool raw_score,
+                         double* out) const {
+  // Predictor over raw feature values (src/application/predictor.hpp), host side: prediction is outside the hot path
+  if (ncol <= max_feature_idx_) Log::Fatal("The number of features in data (%d) is not the same as it was in training data (%d)", ncol, max_feature_idx_ + 1);
+#pragma omp parallel for schedule(static)
+  for (int32_t r = 0; r < nrow; ++r) {
+    std::vector<double> row(ncol);
+    for (int c = 0; c < ncol; ++c) {
+      const int64_t off = is_row_major ? static_cast<int64_t>(r) * ncol + c : static_cast<int64_t>(c) * nrow + r;
+      row[c] = data_type == 0 ? static_cast<double>(static_cast<const float*>(data)[off]) : static_cast<const double*>(data)[off];
+    }
+    double s = 0.0;
+    for (const auto& t : models_) s += t->Predict(row.data());
+    if (!raw_score && objective_function_ != nullptr) {
+      double v;
+      objective_function_->ConvertOutput(&s, &v);
+      s = v;
+    }
+    out[r] = s;
+  }
+}
+
+}  // namespace lgbm_b200

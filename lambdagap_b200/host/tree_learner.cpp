@@ -1,0 +1,236 @@
+// tree_learner.cpp -- B200TreeLearner: the reference's TreeLearner interface over the C ABI, plus the
+// ObjectiveFunction wrapper.
+//
+// Reference: TreeLearner (include/LightGBM/tree_learner.h:27-115), SerialTreeLearner::Train / SplitInner
+// (src/treelearner/serial_tree_learner.cpp:179-245,766-922), GradientDiscretizer::Init random arrays
+// (src/treelearner/gradient_discretizer.cpp:16-41,116), ObjectiveFunction factory
+// (src/objective/objective_function.cpp:19-103).
+#include <algorithm>
+#include <random>
+
+#include "lgbm_host.h"
+
+namespace lgbm_b200 {
+
+// per-iteration start offset of the stochastic-rounding arrays (gradient_discretizer.cpp:23-24,116)
+struct QuantRandomStart {
+  std::mt19937 eng;
+  std::uniform_int_distribution<data_size_t> dist;
+};
+
+TreeLearner* TreeLearner::CreateTreeLearner(const std::string& learner_type, const std::string& device_type,
+                                            const Config* config, gbl_comm* comm) {
+  if (device_type != "cuda" && device_type != "gpu") {
+    Log::Fatal("device_type=%s: only the B200 (cuda) tree learner exists in this library", device_type.c_str());
+  }
+  if (learner_type == "serial") {
+    if (comm != nullptr) Log::Fatal("tree_learner=serial cannot be combined with a communicator; use tree_learner=data");
+    return new B200TreeLearner(config, nullptr);
+  }
+  if (learner_type == "data" || learner_type == "data_parallel") {
+    if (comm == nullptr) Log::Fatal("tree_learner=data needs an initialised communicator (LGBM_NetworkInitWithNccl)");
+    return new B200TreeLearner(config, comm);
+  }
+  Log::Fatal("Unknown tree learner type %s", learner_type.c_str());
+}
+
+B200TreeLearner::~B200TreeLearner() {
+  if (handle_ != nullptr) gbl_learner_free(handle_);
+}
+
+gbl_learner_config B200TreeLearner::MakeConfig() const {
+  gbl_learner_config c;
+  c.num_leaves = config_->num_leaves;
+  c.max_depth = config_->max_depth;
+  c.min_data_in_leaf = config_->min_data_in_leaf;
+  c.use_quantized_grad = config_->use_quantized_grad ? 1 : 0;
+  c.num_grad_quant_bins = config_->num_grad_quant_bins;
+  c.stochastic_rounding = config_->stochastic_rounding ? 1 : 0;
+  c.quant_train_renew_leaf = config_->quant_train_renew_leaf ? 1 : 0;
+  c.is_constant_hessian = is_constant_hessian_ ? 1 : 0;
+  c.min_sum_hessian_in_leaf = config_->min_sum_hessian_in_leaf;
+  c.lambda_l1 = config_->lambda_l1;
+  c.lambda_l2 = config_->lambda_l2;
+  c.min_gain_to_split = config_->min_gain_to_split;
+  c.max_delta_step = config_->max_delta_step;
+  c.path_smooth = config_->path_smooth;
+  return c;
+}
+
+void B200TreeLearner::InitQuantRandom() {
+  // GradientDiscretizer::Init: one mt19937 pair per block of rows, seeded seed + block and seed + block +
+  // num_threads; the values therefore depend on num_threads exactly like the reference's.
+  const data_size_t n = train_data_->num_data();
+  const int num_threads = std::max(1, config_->num_threads);
+  int num_blocks = std::min<int>(num_threads, (n + 512 - 1) / 512);
+  data_size_t block_size = n;
+  if (num_blocks > 1) {
+    block_size = (n + num_blocks - 1) / num_blocks;
+    block_size = (block_size + 31) / 32 * 32;  // SIZE_ALIGNED
+  }
+  std::vector<double> rg(n), rh(n);
+  for (int b = 0; b < num_blocks; ++b) {
+    const data_size_t start = b * block_size;
+    const data_size_t end = std::min(start + block_size, n);
+    std::mt19937 ge(config_->seed + b);
+    std::uniform_real_distribution<double> gd(0.0f, 1.0f);
+    std::mt19937 he(config_->seed + b + num_threads);
+    std::uniform_real_distribution<double> hd(0.0f, 1.0f);
+    for (data_size_t i = start; i < end; ++i) {
+      rg[i] = gd(ge);
+      rh[i] = hd(he);
+    }
+  }
+  GblCheck(gbl_learner_set_quant_random(handle_, rg.data(), rh.data(), n));
+  quant_start_ = std::make_shared<QuantRandomStart>();
+  quant_start_->eng = std::mt19937(config_->seed);
+  quant_start_->dist = std::uniform_int_distribution<data_size_t>(0, n);
+  quant_random_ready_ = true;
+}
+
+void B200TreeLearner::Init(const Dataset* train_data, bool is_constant_hessian) {
+  train_data_ = train_data;
+  is_constant_hessian_ = is_constant_hessian;
+  if (handle_ != nullptr) {
+    gbl_learner_free(handle_);
+    handle_ = nullptr;
+  }
+  gbl_learner_config c = MakeConfig();
+  GblCheck(gbl_learner_create(train_data->device_handle(), &c, comm_, &handle_));
+  records_.resize(config_->num_leaves);
+  quant_random_ready_ = false;
+  if (config_->use_quantized_grad && config_->stochastic_rounding) InitQuantRandom();
+}
+
+void B200TreeLearner::ResetIsConstantHessian(bool is_constant_hessian) {
+  is_constant_hessian_ = is_constant_hessian;
+  gbl_learner_config c = MakeConfig();
+  GblCheck(gbl_learner_reset_config(handle_, &c));
+}
+
+void B200TreeLearner::ResetConfig(const Config* config) {
+  config_ = config;
+  gbl_learner_config c = MakeConfig();
+  GblCheck(gbl_learner_reset_config(handle_, &c));
+  records_.resize(config_->num_leaves);
+}
+
+void B200TreeLearner::SetBaggingData(const Dataset* /*subset*/, const data_size_t* used_indices, data_size_t num_data) {
+  GblCheck(gbl_learner_set_bagging_data(handle_, used_indices, num_data));
+}
+
+Tree* B200TreeLearner::Train(const score_t* gradients, const score_t* hessians, bool /*is_first_tree*/) {
+  if (quant_random_ready_) {
+    GblCheck(gbl_learner_set_quant_random_start(handle_, quant_start_->dist(quant_start_->eng)));
+  }
+  gbl_tree_result res;
+  GblCheck(gbl_learner_train(handle_, gradients, hessians, &res, records_.data()));
+  std::unique_ptr<Tree> tree(new Tree(config_->num_leaves));
+  tree->SetLeafOutput(0, res.root_output);  // serial_tree_learner.cpp:205-208
+  for (int k = 0; k < res.num_splits; ++k) {
+    const gbl_split_record& r = records_[k];
+    const BinMapper* m = train_data_->FeatureBinMapper(r.feature);
+    // SerialTreeLearner::SplitInner -> Tree::Split, serial_tree_learner.cpp:798-810
+    tree->Split(r.leaf, r.feature, r.real_feature, r.threshold_bin, train_data_->RealThreshold(r.feature, r.threshold_bin),
+                r.left_output, r.right_output, r.left_count, r.right_count, r.left_sum_hessian, r.right_sum_hessian,
+                static_cast<float>(r.gain + config_->min_gain_to_split), m->missing_type(), r.default_left != 0);
+  }
+  if (res.num_splits == 0) Log::Warning("No further splits with positive gain");
+  return tree.release();
+}
+
+void B200TreeLearner::AddPredictionToScore(const Tree* tree, double* out_score) const {
+  if (tree->num_leaves() <= 1) return;  // serial_tree_learner.h:101-103
+  GblCheck(gbl_learner_add_prediction_to_score(handle_, tree->leaf_values().data(), tree->num_leaves(), out_score));
+}
+
+// ------------------------------------------------------------------------------------------- objectives
+static const char* kRankTargets[] = {
+    // rank_objective.hpp:22-41, same order as the reference's target list
+    "ndcg", "lambdaloss-ndcg", "lambdaloss-ndcg-plus-plus", "bndcg", "lambdaloss-bndcg", "lambdaloss-bndcg-plus-plus",
+    "precision", "arpk", "lambdaloss-arp1", "lambdaloss-arp2", "ranknet", "bin-ranknet", "lambdagap-s", "lambdagap-x",
+    "lambdagap-s-plus", "lambdagap-x-plus", "lambdagap-s-plus-plus", "lambdagap-x-plus-plus"};
+
+int RankTargetIndex(const std::string& name) {
+  for (int i = 0; i < 18; ++i) {
+    if (name == kRankTargets[i]) return i;
+  }
+  return -1;
+}
+
+ObjectiveFunction* ObjectiveFunction::CreateObjectiveFunction(const std::string& type, const Config& config) {
+  if (type == "custom") return nullptr;
+  if (type != "regression" && type != "binary" && type != "lambdarank") {
+    Log::Fatal("Unknown objective type name: %s (the B200 library provides regression, binary, lambdarank)", type.c_str());
+  }
+  if (type == "lambdarank" && RankTargetIndex(config.lambdarank_target) < 0) {
+    Log::Fatal("Unknown lambdarank_target: %s", config.lambdarank_target.c_str());
+  }
+  if (type == "regression" && config.reg_sqrt) Log::Fatal("reg_sqrt is not supported by the B200 library");
+  ObjectiveFunction* o = new ObjectiveFunction();
+  o->name_ = type;
+  o->config_ = config;
+  return o;
+}
+
+ObjectiveFunction::~ObjectiveFunction() {
+  if (handle_ != nullptr) gbl_objective_free(handle_);
+}
+
+void ObjectiveFunction::Init(const Metadata& metadata, data_size_t num_data, int device_id) {
+  if (static_cast<data_size_t>(metadata.label.size()) != num_data) Log::Fatal("Objective: label not set (use LGBM_DatasetSetField)");
+  gbl_objective_config c;
+  c.kind = name_ == "regression" ? GBL_OBJ_REGRESSION_L2 : (name_ == "binary" ? GBL_OBJ_BINARY : GBL_OBJ_LAMBDARANK);
+  c.lambdarank_target = std::max(0, RankTargetIndex(config_.lambdarank_target));
+  c.lambdarank_truncation_level = config_.lambdarank_truncation_level;
+  c.lambdarank_norm = config_.lambdarank_norm ? 1 : 0;
+  c.sigmoid = config_.sigmoid;
+  c.lambdagap_weight = config_.lambdagap_weight;
+  c.is_unbalance = config_.is_unbalance ? 1 : 0;
+  c.reserved = 0;
+  c.scale_pos_weight = config_.scale_pos_weight;
+  c.num_label_gain = static_cast<int>(config_.label_gain.size());
+  c.reserved2 = 0;
+  c.label_gain = config_.label_gain.empty() ? nullptr : config_.label_gain.data();
+  if (name_ == "lambdarank" && metadata.query_boundaries.empty()) Log::Fatal("Ranking tasks require query information");
+  GblCheck(gbl_objective_create(&c, num_data, metadata.label.data(),
+                                metadata.weights.empty() ? nullptr : metadata.weights.data(),
+                                metadata.query_boundaries.empty() ? nullptr : metadata.query_boundaries.data(),
+                                metadata.num_queries(), device_id, &handle_));
+}
+
+void ObjectiveFunction::GetGradients(const double* score, score_t* gradients, score_t* hessians, void* stream) const {
+  GblCheck(gbl_objective_get_gradients(handle_, score, gradients, hessians, stream));
+}
+
+double ObjectiveFunction::BoostFromScore(int /*class_id*/) const {
+  double v = 0.0;
+  GblCheck(gbl_objective_boost_from_score(handle_, &v));
+  return v;
+}
+
+bool ObjectiveFunction::IsConstantHessian() const {
+  int32_t v = 0;
+  GblCheck(gbl_objective_is_constant_hessian(handle_, &v));
+  return v != 0;
+}
+
+std::string ObjectiveFunction::ToString() const {
+  // BinaryLogloss::ToString (binary_objective.hpp:176-181), RegressionL2loss (:139-146), LambdarankNDCG
+  if (name_ == "binary") {
+    char buf[64];
+    snprintf(buf, sizeof(buf), "binary sigmoid:%g", config_.sigmoid);
+    return buf;
+  }
+  return name_;
+}
+
+void ObjectiveFunction::ConvertOutput(const double* input, double* output) const {
+  if (name_ == "binary") {
+    output[0] = 1.0f / (1.0f + std::exp(-config_.sigmoid * input[0]));
+  } else {
+    output[0] = input[0];
+  }
+}
+
+}  // namespace lgbm_b200

@@ -133,6 +133,38 @@ class RefBooster:
                                             out.ctypes.data_as(ctypes.c_void_p)))
         return out
 
+    def train_scores_raw(self):
+        """Raw (unconverted) training scores: GetPredict applies ConvertOutput, so invert the sigmoid for binary."""
+        s = self.train_scores()
+        if self._objective() == "binary":
+            s = np.log(s / (1.0 - s))
+        return s
+
+    def _objective(self):
+        for line in self.model_string().split("\n"):
+            if line.startswith("objective="):
+                return line.split("=", 1)[1].split()[0]
+        return ""
+
+    @classmethod
+    def from_model_string(cls, text):
+        self = cls.__new__(cls)
+        self.ds = None
+        self.handle = ctypes.c_void_p()
+        it = ctypes.c_int(0)
+        _check(lib().LGBM_BoosterLoadModelFromString(ctypes.c_char_p(text.encode()), ctypes.byref(it), ctypes.byref(self.handle)))
+        return self
+
+    def predict(self, X, raw_score=False):
+        X = np.ascontiguousarray(X, dtype=np.float64)
+        out = np.zeros(X.shape[0], dtype=np.float64)
+        n = ctypes.c_int64(0)
+        _check(lib().LGBM_BoosterPredictForMat(self.handle, X.ctypes.data_as(ctypes.c_void_p), ctypes.c_int(C_API_DTYPE_FLOAT64),
+                                               ctypes.c_int32(X.shape[0]), ctypes.c_int32(X.shape[1]), ctypes.c_int(1),
+                                               ctypes.c_int(1 if raw_score else 0), ctypes.c_int(0), ctypes.c_int(-1),
+                                               ctypes.c_char_p(b"num_threads=4"), ctypes.byref(n), out.ctypes.data_as(ctypes.c_void_p)))
+        return out
+
     def model_string(self):
         need = ctypes.c_int64(0)
         buf = ctypes.create_string_buffer(1 << 20)
