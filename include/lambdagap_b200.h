@@ -139,6 +139,10 @@ GBL_API int gbl_dataset_get_feature_bins_rowmajor(const gbl_dataset* ds, int32_t
 GBL_API int gbl_comm_get_unique_id(uint8_t out_id[128]);
 GBL_API int gbl_comm_create(const uint8_t id[128], int32_t num_ranks, int32_t rank, int32_t device_id, gbl_comm** out);
 GBL_API int gbl_comm_free(gbl_comm* comm);
+/* Network::GlobalSyncUpBySum / ByMax / ByMean on small host vectors (include/LightGBM/network.h:180-260), used by
+ * the host layer for init scores and label statistics.  op: 0 = sum, 1 = max. */
+GBL_API int gbl_comm_allreduce_host_f64(gbl_comm* comm, double* inout_host, int32_t n, int32_t op);
+GBL_API int gbl_comm_info(const gbl_comm* comm, int32_t* out_num_ranks, int32_t* out_rank);
 
 /* ---------------------------------------------------------------- src/treelearner: the tree learner */
 /* TreeLearner::Init (include/LightGBM/tree_learner.h:37).  `comm` NULL = single GPU (SerialTreeLearner
@@ -215,6 +219,10 @@ typedef struct gbl_profile {
   int64_t trees;
 } gbl_profile;
 GBL_API int gbl_learner_set_profiling(gbl_learner* learner, int32_t enabled);
+/* CUDA-event stopwatch on the learner's stream (the stream every kernel of this library is launched on):
+ * record slot 0..7, then elapsed milliseconds between two recorded slots (synchronises on the later one). */
+GBL_API int gbl_learner_timer_record(gbl_learner* learner, int32_t slot);
+GBL_API int gbl_learner_timer_elapsed_ms(gbl_learner* learner, int32_t slot_begin, int32_t slot_end, double* out_ms);
 GBL_API int gbl_learner_get_profile(gbl_learner* learner, gbl_profile* out, int32_t reset);
 
 /* ---------------------------------------------------------------- src/objective */

@@ -32,6 +32,13 @@ LGBM_B200_EXPORT const char* LGBM_GetLastError(void);
 LGBM_B200_EXPORT int LGBM_DatasetCreateFromMat(const void* data, int data_type, int32_t nrow, int32_t ncol,
                                                int is_row_major, const char* parameters,
                                                const DatasetHandle reference, DatasetHandle* out);
+/* Analogue of LGBM_DatasetCreateFromSampledColumn (src/c_api.cpp:1063-1100) for dense matrices: bin mappers are
+ * found from `sample` (every row, same dtype / layout as data), then `data` (this rank's shard of `num_total_row`
+ * rows overall) is binned.  Every rank that passes the same sample derives identical mappers. */
+LGBM_B200_EXPORT int LGBM_DatasetCreateFromMatWithSample(const void* data, int data_type, int32_t nrow, int32_t ncol,
+                                                         int is_row_major, const void* sample, int32_t sample_nrow,
+                                                         int64_t num_total_row, const char* parameters,
+                                                         DatasetHandle* out);
 /* src/c_api.cpp:1760 (c_api.h:552) */
 LGBM_B200_EXPORT int LGBM_DatasetSetField(DatasetHandle handle, const char* field_name, const void* field_data,
                                           int num_element, int type);
@@ -71,6 +78,8 @@ LGBM_B200_EXPORT int LGBM_NetworkGetNcclUniqueId(uint8_t out_id[128]);
 LGBM_B200_EXPORT int LGBM_NetworkInitWithNccl(const uint8_t id[128], int num_machines, int rank, int device_id);
 /* src/c_api.cpp:2781 */
 LGBM_B200_EXPORT int LGBM_NetworkFree(void);
+/* not in the reference: the C-ABI learner handle behind a booster (gbl_learner*), for timers and profiling */
+LGBM_B200_EXPORT int LGBM_BoosterGetLearnerHandle(BoosterHandle handle, void** out_learner);
 /* not in the reference: raw (unconverted) training scores, device -> host */
 LGBM_B200_EXPORT int LGBM_BoosterGetTrainScoreRaw(BoosterHandle handle, int64_t* out_len, double* out_result);
 

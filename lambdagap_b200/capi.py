@@ -69,14 +69,15 @@ EXPORTED_SYMBOLS = [
     "gbl_last_error", "gbl_device_count", "gbl_kernel_launch_count",
     "gbl_dataset_create_from_bins", "gbl_dataset_create_from_mat_f32", "gbl_dataset_free", "gbl_dataset_num_data",
     "gbl_dataset_get_feature_bins", "gbl_dataset_get_feature_bins_rowmajor",
-    "gbl_comm_get_unique_id", "gbl_comm_create", "gbl_comm_free",
+    "gbl_comm_get_unique_id", "gbl_comm_create", "gbl_comm_free", "gbl_comm_allreduce_host_f64", "gbl_comm_info",
     "gbl_learner_create", "gbl_learner_free", "gbl_learner_reset_config", "gbl_learner_set_feature_mask",
     "gbl_learner_set_bagging_data", "gbl_learner_set_quant_random", "gbl_learner_set_quant_random_start",
     "gbl_learner_train", "gbl_learner_train_host", "gbl_learner_train_async", "gbl_learner_train_finish",
     "gbl_learner_add_prediction_to_score", "gbl_learner_add_prediction_to_score_dev",
     "gbl_learner_get_leaf_assignment", "gbl_learner_get_leaf_indices", "gbl_learner_get_histogram",
     "gbl_learner_get_discretized", "gbl_learner_histogram_words", "gbl_learner_construct_histogram",
-    "gbl_learner_stream", "gbl_learner_set_profiling", "gbl_learner_get_profile",
+    "gbl_learner_stream", "gbl_learner_set_profiling", "gbl_learner_get_profile", "gbl_learner_timer_record",
+    "gbl_learner_timer_elapsed_ms",
     "gbl_objective_create", "gbl_objective_free", "gbl_objective_get_gradients", "gbl_objective_boost_from_score",
     "gbl_objective_is_constant_hessian",
     "gbl_device_malloc", "gbl_device_free", "gbl_memcpy_h2d", "gbl_memcpy_d2h", "gbl_device_fill_f64",
@@ -395,6 +396,14 @@ class Learner:
 
     def stream(self):
         return lib().gbl_learner_stream(self.handle)
+
+    def timer_record(self, slot):
+        check(lib().gbl_learner_timer_record(self.handle, ctypes.c_int32(slot)))
+
+    def timer_elapsed_ms(self, a, b):
+        out = ctypes.c_double(0)
+        check(lib().gbl_learner_timer_elapsed_ms(self.handle, ctypes.c_int32(a), ctypes.c_int32(b), ctypes.byref(out)))
+        return out.value
 
     def set_profiling(self, on):
         check(lib().gbl_learner_set_profiling(self.handle, ctypes.c_int32(1 if on else 0)))

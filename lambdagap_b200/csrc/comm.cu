@@ -117,6 +117,30 @@ int gbl_comm_create(const uint8_t id[128], int32_t num_ranks, int32_t rank, int3
   GBL_API_END();
 }
 
+int gbl_comm_allreduce_host_f64(gbl_comm* comm, double* inout_host, int32_t n, int32_t op) {
+  GBL_API_BEGIN();
+  Comm* c = reinterpret_cast<Comm*>(comm);
+  if (c == nullptr || inout_host == nullptr || n <= 0) fatal("gbl_comm_allreduce_host_f64: bad argument");
+  DeviceGuard guard(c->device);
+  double* d = nullptr;
+  GBL_CUDA(cudaMalloc(&d, sizeof(double) * n));
+  GBL_CUDA(cudaMemcpy(d, inout_host, sizeof(double) * n, cudaMemcpyHostToDevice));
+  comm_allreduce_f64(c, d, n, op == 1 ? RedOp::kMax : RedOp::kSum, 0);
+  GBL_CUDA(cudaStreamSynchronize(0));
+  GBL_CUDA(cudaMemcpy(inout_host, d, sizeof(double) * n, cudaMemcpyDeviceToHost));
+  cudaFree(d);
+  GBL_API_END();
+}
+
+int gbl_comm_info(const gbl_comm* comm, int32_t* out_num_ranks, int32_t* out_rank) {
+  GBL_API_BEGIN();
+  const Comm* c = reinterpret_cast<const Comm*>(comm);
+  if (c == nullptr) fatal("gbl_comm_info: null communicator");
+  if (out_num_ranks) *out_num_ranks = c->num_ranks;
+  if (out_rank) *out_rank = c->rank;
+  GBL_API_END();
+}
+
 int gbl_comm_free(gbl_comm* comm) {
   GBL_API_BEGIN();
   comm_free(reinterpret_cast<Comm*>(comm));

@@ -65,6 +65,8 @@ struct Learner {
   std::vector<int> ev_stage;       // stage id per event pair
   size_t ev_used = 0;
   gbl_profile prof{};
+  cudaEvent_t timer[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  long long graph_kernel_nodes = 0;  // kernels inside the captured graph (launch accounting)
 };
 
 enum Stage { kStageHist = 0, kStageFind = 1, kStagePart = 2, kStageOther = 3, kStageComm = 4 };
@@ -252,6 +254,9 @@ static void learner_free(Learner* L) {
   cudaFree(L->tap_hist);
   if (L->ts_pinned) cudaFreeHost(L->ts_pinned);
   for (cudaEvent_t e : L->ev) cudaEventDestroy(e);
+  for (cudaEvent_t e : L->timer) {
+    if (e != nullptr) cudaEventDestroy(e);
+  }
   cudaStreamDestroy(L->stream);
   delete L;
 }
@@ -325,6 +330,7 @@ static void train_async(Learner* L, const float* grad_dev, const float* hess_dev
     if (stale) {
       drop_graph(L);
       cudaGraph_t graph = nullptr;
+      const long long launches_before = g_kernel_launches.load();
       GBL_CUDA(cudaStreamBeginCapture(L->stream, cudaStreamCaptureModeThreadLocal));
       try {
         enqueue_tree(L, L->stream);
@@ -336,6 +342,9 @@ static void train_async(Learner* L, const float* grad_dev, const float* hess_dev
       GBL_CUDA(cudaStreamEndCapture(L->stream, &graph));
       GBL_CUDA(cudaGraphInstantiate(&L->graph_exec, graph, 0));
       cudaGraphDestroy(graph);
+      // launches "made" during capture only built graph nodes: count them once per replay instead
+      L->graph_kernel_nodes = g_kernel_launches.load() - launches_before;
+      g_kernel_launches.store(launches_before);
       L->graph_grad = grad_dev;
       L->graph_hess = hess_dev;
       L->graph_rand_start = d.rand_start;
@@ -343,6 +352,7 @@ static void train_async(Learner* L, const float* grad_dev, const float* hess_dev
       L->graph_bag_count = L->bag_count;
     }
     GBL_CUDA(cudaGraphLaunch(L->graph_exec, L->stream));
+    g_kernel_launches.fetch_add(L->graph_kernel_nodes, std::memory_order_relaxed);
   } else {
     enqueue_tree(L, L->stream);
   }
@@ -694,6 +704,30 @@ int gbl_learner_set_profiling(gbl_learner* learner, int32_t enabled) {
   GBL_CUDA(cudaStreamSynchronize(L->stream));
   drop_graph(L);
   L->profiling = enabled != 0;
+  GBL_API_END();
+}
+
+int gbl_learner_timer_record(gbl_learner* learner, int32_t slot) {
+  GBL_API_BEGIN();
+  Learner* L = LEARNER(learner);
+  if (L == nullptr || slot < 0 || slot >= 8) fatal("gbl_learner_timer_record: bad argument");
+  DeviceGuard guard(L->ds->device);
+  if (L->timer[slot] == nullptr) GBL_CUDA(cudaEventCreate(&L->timer[slot]));
+  GBL_CUDA(cudaEventRecord(L->timer[slot], L->stream));
+  GBL_API_END();
+}
+
+int gbl_learner_timer_elapsed_ms(gbl_learner* learner, int32_t slot_begin, int32_t slot_end, double* out_ms) {
+  GBL_API_BEGIN();
+  Learner* L = LEARNER(learner);
+  if (L == nullptr || out_ms == nullptr || slot_begin < 0 || slot_begin >= 8 || slot_end < 0 || slot_end >= 8 ||
+      L->timer[slot_begin] == nullptr || L->timer[slot_end] == nullptr)
+    fatal("gbl_learner_timer_elapsed_ms: bad argument");
+  DeviceGuard guard(L->ds->device);
+  GBL_CUDA(cudaEventSynchronize(L->timer[slot_end]));
+  float ms = 0.f;
+  GBL_CUDA(cudaEventElapsedTime(&ms, L->timer[slot_begin], L->timer[slot_end]));
+  *out_ms = ms;
   GBL_API_END();
 }
 

@@ -20,6 +20,7 @@ LGBM_EXPORTED_SYMBOLS = [
     "LGBM_BoosterNumberOfTotalModel", "LGBM_BoosterGetNumPredict", "LGBM_BoosterGetPredict",
     "LGBM_BoosterPredictForMat", "LGBM_BoosterSaveModelToString", "LGBM_NetworkGetNcclUniqueId",
     "LGBM_NetworkInitWithNccl", "LGBM_NetworkFree", "LGBM_BoosterGetTrainScoreRaw",
+    "LGBM_DatasetCreateFromMatWithSample", "LGBM_BoosterGetLearnerHandle",
 ]
 
 _lib = None
@@ -56,17 +57,26 @@ def _params(p):
 
 
 class Dataset:
-    def __init__(self, X, label=None, group=None, weight=None, params=None, reference=None):
+    def __init__(self, X, label=None, group=None, weight=None, params=None, reference=None, bin_sample=None,
+                 num_total_rows=None):
         X = np.ascontiguousarray(X)
         if X.dtype not in (np.float32, np.float64):
             X = X.astype(np.float32)
         self.n, self.f = X.shape
         self.handle = ctypes.c_void_p()
         dt = C_API_DTYPE_FLOAT32 if X.dtype == np.float32 else C_API_DTYPE_FLOAT64
-        _check(lib().LGBM_DatasetCreateFromMat(
-            X.ctypes.data_as(ctypes.c_void_p), ctypes.c_int(dt), ctypes.c_int32(self.n), ctypes.c_int32(self.f),
-            ctypes.c_int(1), ctypes.c_char_p(_params(params)), reference.handle if reference is not None else None,
-            ctypes.byref(self.handle)))
+        if bin_sample is not None:
+            S = np.ascontiguousarray(bin_sample, dtype=X.dtype)
+            _check(lib().LGBM_DatasetCreateFromMatWithSample(
+                X.ctypes.data_as(ctypes.c_void_p), ctypes.c_int(dt), ctypes.c_int32(self.n), ctypes.c_int32(self.f),
+                ctypes.c_int(1), S.ctypes.data_as(ctypes.c_void_p), ctypes.c_int32(S.shape[0]),
+                ctypes.c_int64(num_total_rows if num_total_rows is not None else self.n),
+                ctypes.c_char_p(_params(params)), ctypes.byref(self.handle)))
+        else:
+            _check(lib().LGBM_DatasetCreateFromMat(
+                X.ctypes.data_as(ctypes.c_void_p), ctypes.c_int(dt), ctypes.c_int32(self.n), ctypes.c_int32(self.f),
+                ctypes.c_int(1), ctypes.c_char_p(_params(params)), reference.handle if reference is not None else None,
+                ctypes.byref(self.handle)))
         if label is not None:
             self.set_field("label", np.asarray(label, dtype=np.float32))
         if weight is not None:
@@ -105,6 +115,16 @@ class Booster:
         _check(lib().LGBM_BoosterUpdateOneIterCustom(self.handle, grad.ctypes.data_as(ctypes.c_void_p),
                                                      hess.ctypes.data_as(ctypes.c_void_p), ctypes.byref(fin)))
         return fin.value
+
+    def learner(self):
+        """The C-ABI learner behind this booster, wrapped for timers / profiling (capi.Learner methods)."""
+        h = ctypes.c_void_p()
+        _check(lib().LGBM_BoosterGetLearnerHandle(self.handle, ctypes.byref(h)))
+        lrn = capi.Learner.__new__(capi.Learner)
+        lrn.handle = h
+        lrn.ds = None
+        lrn.cfg = None
+        return lrn
 
     def current_iteration(self):
         out = ctypes.c_int(0)

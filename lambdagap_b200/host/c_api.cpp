@@ -62,6 +62,18 @@ int LGBM_DatasetCreateFromMat(const void* data, int data_type, int32_t nrow, int
   API_END();
 }
 
+int LGBM_DatasetCreateFromMatWithSample(const void* data, int data_type, int32_t nrow, int32_t ncol, int is_row_major,
+                                        const void* sample, int32_t sample_nrow, int64_t num_total_row,
+                                        const char* parameters, DatasetHandle* out) {
+  API_BEGIN();
+  Config config;
+  config.Set(parameters ? parameters : "");
+  if (sample == nullptr || sample_nrow <= 0) Log::Fatal("LGBM_DatasetCreateFromMatWithSample: empty sample");
+  *out = Dataset::CreateFromMatWithSample(data, data_type, nrow, ncol, is_row_major, sample, sample_nrow, num_total_row,
+                                          config);
+  API_END();
+}
+
 int LGBM_DatasetSetField(DatasetHandle handle, const char* field_name, const void* field_data, int num_element,
                          int type) {
   API_BEGIN();
@@ -138,6 +150,15 @@ int LGBM_BoosterGetPredict(BoosterHandle handle, int data_idx, int64_t* out_len,
   Booster* b = reinterpret_cast<Booster*>(handle);
   std::lock_guard<std::mutex> lock(b->mutex);
   b->boosting->GetPredictAt(data_idx, out_result, out_len);
+  API_END();
+}
+
+int LGBM_BoosterGetLearnerHandle(BoosterHandle handle, void** out_learner) {
+  API_BEGIN();
+  Booster* b = reinterpret_cast<Booster*>(handle);
+  B200TreeLearner* bl = dynamic_cast<B200TreeLearner*>(b->boosting->tree_learner());
+  if (bl == nullptr) Log::Fatal("booster has no B200 tree learner");
+  *out_learner = bl->handle();
   API_END();
 }
 

@@ -27,6 +27,20 @@ Dataset::~Dataset() {
 
 Dataset* Dataset::CreateFromMat(const void* data, int data_type, int32_t nrow, int32_t ncol, int is_row_major,
                                 const Config& config, const Dataset* reference) {
+  return CreateFromMatWithSample(data, data_type, nrow, ncol, is_row_major, nullptr, 0, nrow, config,
+                                 reference);
+}
+
+Dataset* Dataset::CreateFromMatWithSample(const void* data, int data_type, int32_t nrow, int32_t ncol, int is_row_major,
+                                          const void* sample, int32_t sample_nrow, int64_t num_total_rows,
+                                          const Config& config) {
+  return CreateFromMatWithSample(data, data_type, nrow, ncol, is_row_major, sample, sample_nrow, num_total_rows, config,
+                                 nullptr);
+}
+
+Dataset* Dataset::CreateFromMatWithSample(const void* data, int data_type, int32_t nrow, int32_t ncol, int is_row_major,
+                                          const void* sample, int32_t sample_nrow, int64_t num_total_rows,
+                                          const Config& config, const Dataset* reference) {
   if (data == nullptr) Log::Fatal("LGBM_DatasetCreateFromMat: data is null");
   if (data_type != kDtypeFloat32 && data_type != kDtypeFloat64) Log::Fatal("Unknown data type in RowFunctionFromDenseMatric");
   if (nrow <= 0 || ncol <= 0) Log::Fatal("LGBM_DatasetCreateFromMat: empty matrix");
@@ -36,20 +50,29 @@ Dataset* Dataset::CreateFromMat(const void* data, int data_type, int32_t nrow, i
   ds->device_id_ = config.gpu_device_id < 0 ? 0 : config.gpu_device_id;
 
   if (reference == nullptr) {
-    Random rand(config.data_random_seed);
-    const int sample_cnt = nrow < config.bin_construct_sample_cnt ? nrow : config.bin_construct_sample_cnt;
-    const std::vector<int> sample_indices = rand.Sample(nrow, sample_cnt);
+    std::vector<int> sample_indices;
+    const void* src = data;
+    int32_t src_rows = nrow;
+    if (sample != nullptr) {  // explicit sample: every row of it
+      src = sample;
+      src_rows = sample_nrow;
+      for (int i = 0; i < sample_nrow; ++i) sample_indices.push_back(i);
+    } else {
+      Random rand(config.data_random_seed);
+      const int sample_cnt = nrow < config.bin_construct_sample_cnt ? nrow : config.bin_construct_sample_cnt;
+      sample_indices = rand.Sample(nrow, sample_cnt);
+    }
     const size_t total_sample_size = sample_indices.size();
     // dataset_loader.cpp:623-624
     const data_size_t filter_cnt = static_cast<data_size_t>(
-        static_cast<double>(config.min_data_in_leaf * total_sample_size) / nrow);
+        static_cast<double>(config.min_data_in_leaf * total_sample_size) / num_total_rows);
     ds->all_bin_mappers_.resize(ncol);
 #pragma omp parallel for schedule(guided)
     for (int c = 0; c < ncol; ++c) {
       std::vector<double> vals;
       vals.reserve(total_sample_size);
       for (size_t i = 0; i < total_sample_size; ++i) {
-        const double v = Cell(data, data_type, nrow, ncol, is_row_major, sample_indices[i], c);
+        const double v = Cell(src, data_type, src_rows, ncol, is_row_major, sample_indices[i], c);
         if (std::fabs(v) > kZeroThreshold || std::isnan(v)) vals.push_back(v);
       }
       std::shared_ptr<BinMapper> m(new BinMapper());

@@ -24,6 +24,7 @@ void GBDT::Init(const Config* config, const Dataset* train_data, ObjectiveFuncti
   config_ = config;
   train_data_ = train_data;
   objective_function_ = objective;
+  comm_ = comm;
   num_data_ = train_data->num_data();
   shrinkage_rate_ = config->learning_rate;
   device_id_ = train_data->device_id();
@@ -50,7 +51,14 @@ void GBDT::Init(const Config* config, const Dataset* train_data, ObjectiveFuncti
 double GBDT::BoostFromAverage() {
   // gbdt.cpp:319-343 (single GPU: no Network::GlobalSyncUpByMean)
   if (models_.empty() && !has_init_score_ && objective_function_ != nullptr && config_->boost_from_average) {
-    const double init_score = objective_function_->BoostFromScore(0);
+    double init_score = objective_function_->BoostFromScore(0);
+    if (comm_ != nullptr) {
+      // ObtainAutomaticInitialScore: Network::GlobalSyncUpByMean (gbdt.cpp:306-317)
+      int32_t nranks = 1;
+      GblCheck(gbl_comm_info(comm_, &nranks, nullptr));
+      GblCheck(gbl_comm_allreduce_host_f64(comm_, &init_score, 1, 0));
+      init_score /= nranks;
+    }
     if (std::fabs(init_score) > kEpsilon) {
       // ScoreUpdater::AddScore(val): one fill since all scores are still zero
       GblCheck(gbl_device_fill_f64(device_id_, score_dev_, init_score, num_data_));
@@ -76,12 +84,24 @@ bool GBDT::TrainOneIter(const score_t* gradients, const score_t* hessians) {
     GblCheck(gbl_memcpy_h2d(device_id_, hess_dev_, hessians, sizeof(float) * num_data_));
   }
   const bool is_first_tree = models_.empty();
-  std::unique_ptr<Tree> new_tree(tree_learner_->Train(grad_dev_, hess_dev_, is_first_tree));
+  std::unique_ptr<Tree> new_tree;
+  bool score_updated = false;
+  if (B200TreeLearner* bl = dynamic_cast<B200TreeLearner*>(tree_learner_.get())) {
+    // tree + score update enqueued back to back; the host waits once, for the split records.  A tree without
+    // splits has all-zero device leaf outputs, so the update is a no-op in that case (UpdateScore is skipped for
+    // such trees in the reference, gbdt.cpp:408-419).
+    bl->TrainAsync(grad_dev_, hess_dev_);
+    bl->AddPredictionToScoreAsync(shrinkage_rate_, score_dev_);
+    new_tree.reset(bl->FinishTrain());
+    score_updated = true;
+  } else {
+    new_tree.reset(tree_learner_->Train(grad_dev_, hess_dev_, is_first_tree));
+  }
   bool should_continue = false;
   if (new_tree->num_leaves() > 1) {
     should_continue = true;
     new_tree->Shrinkage(shrinkage_rate_);
-    tree_learner_->AddPredictionToScore(new_tree.get(), score_dev_);  // UpdateScore
+    if (!score_updated) tree_learner_->AddPredictionToScore(new_tree.get(), score_dev_);  // UpdateScore
     if (std::fabs(init_score) > kEpsilon) new_tree->AddBias(init_score);
   } else {
     if (models_.empty()) {

@@ -178,6 +178,15 @@ class Dataset {
   // the device.  `reference` != nullptr aligns the bin mappers with another dataset (validation data).
   static Dataset* CreateFromMat(const void* data, int data_type, int32_t nrow, int32_t ncol, int is_row_major,
                                 const Config& config, const Dataset* reference);
+  // Same, but the bin mappers come from an explicit sample matrix (every row of it) instead of rows sampled from
+  // `data`: the role LGBM_DatasetCreateFromSampledColumn (src/c_api.cpp:1063-1100) plays for distributed loading,
+  // where every rank must derive identical mappers before binning its own row shard.
+  static Dataset* CreateFromMatWithSample(const void* data, int data_type, int32_t nrow, int32_t ncol, int is_row_major,
+                                          const void* sample, int32_t sample_nrow, int64_t num_total_rows,
+                                          const Config& config);
+  static Dataset* CreateFromMatWithSample(const void* data, int data_type, int32_t nrow, int32_t ncol, int is_row_major,
+                                          const void* sample, int32_t sample_nrow, int64_t num_total_rows,
+                                          const Config& config, const Dataset* reference);
   void SetField(const char* name, const void* data, int num_element, int type);
   data_size_t num_data() const { return num_data_; }
   int num_features() const { return static_cast<int>(used_feature_map_inv_.size()); }
@@ -292,6 +301,11 @@ class B200TreeLearner : public TreeLearner {
   void SetBaggingData(const Dataset* subset, const data_size_t* used_indices, data_size_t num_data) override;
   void AddPredictionToScore(const Tree* tree, double* out_score) const override;
   gbl_learner* handle() const { return handle_; }
+  // device-resident pipeline used by GBDT: enqueue the tree, update the scores from the leaf outputs that are
+  // still on the device, and only then wait for the split records
+  void TrainAsync(const score_t* gradients, const score_t* hessians);
+  void AddPredictionToScoreAsync(double shrinkage, double* out_score) const;
+  Tree* FinishTrain();
 
  private:
   gbl_learner_config MakeConfig() const;
@@ -330,6 +344,7 @@ class GBDT {
 
  private:
   double BoostFromAverage();
+  gbl_comm* comm_ = nullptr;
   const Config* config_ = nullptr;
   const Dataset* train_data_ = nullptr;
   ObjectiveFunction* objective_function_ = nullptr;

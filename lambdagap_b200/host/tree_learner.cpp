@@ -120,11 +120,24 @@ void B200TreeLearner::SetBaggingData(const Dataset* /*subset*/, const data_size_
 }
 
 Tree* B200TreeLearner::Train(const score_t* gradients, const score_t* hessians, bool /*is_first_tree*/) {
+  TrainAsync(gradients, hessians);
+  return FinishTrain();
+}
+
+void B200TreeLearner::TrainAsync(const score_t* gradients, const score_t* hessians) {
   if (quant_random_ready_) {
     GblCheck(gbl_learner_set_quant_random_start(handle_, quant_start_->dist(quant_start_->eng)));
   }
+  GblCheck(gbl_learner_train_async(handle_, gradients, hessians));
+}
+
+void B200TreeLearner::AddPredictionToScoreAsync(double shrinkage, double* out_score) const {
+  GblCheck(gbl_learner_add_prediction_to_score_dev(handle_, shrinkage, 0.0, out_score));
+}
+
+Tree* B200TreeLearner::FinishTrain() {
   gbl_tree_result res;
-  GblCheck(gbl_learner_train(handle_, gradients, hessians, &res, records_.data()));
+  GblCheck(gbl_learner_train_finish(handle_, &res, records_.data()));
   std::unique_ptr<Tree> tree(new Tree(config_->num_leaves));
   tree->SetLeafOutput(0, res.root_output);  // serial_tree_learner.cpp:205-208
   for (int k = 0; k < res.num_splits; ++k) {
