@@ -225,6 +225,20 @@ GBL_API int gbl_learner_timer_record(gbl_learner* learner, int32_t slot);
 GBL_API int gbl_learner_timer_elapsed_ms(gbl_learner* learner, int32_t slot_begin, int32_t slot_end, double* out_ms);
 GBL_API int gbl_learner_get_profile(gbl_learner* learner, gbl_profile* out, int32_t reset);
 
+/* No counterpart in the reference.  The same stable row partition the learner performs for a split
+ * (left block first, both blocks in their original order; missing rows follow default_left), for callers that may
+ * not allocate device memory: hosts whose own pool allocator owns all of HBM, and latency-critical callers that
+ * cannot take cudaMalloc's device-wide synchronisation.  The per-CTA scratch lives in a static device array inside
+ * the library (16.25 KB per GPU, held until process exit), so the call performs no allocation of any kind; the
+ * caller supplies every buffer: `indices_dev` (NULL = rows 0..num_indices-1), `out_indices_dev[num_indices]`,
+ * `out_left_count_dev[1]`, all on the dataset's device.  Limits and rules: at most 16,777,216 rows per call (more is
+ * refused with -1); all calls on one GPU share the scratch, so calls that overlap on the GPU race -- issue them
+ * one after another; the first call made on a device also resolves the scratch address and should come before any
+ * stream capture.  Asynchronous on `stream` (NULL = default stream). */
+GBL_API int gbl_partition_rows_noalloc(const gbl_dataset* ds, int32_t feature, uint32_t threshold_bin,
+                                       int32_t default_left, const int32_t* indices_dev, int32_t num_indices,
+                                       int32_t* out_indices_dev, int32_t* out_left_count_dev, void* stream);
+
 /* ---------------------------------------------------------------- src/objective */
 typedef struct gbl_objective_config {
   int32_t kind;                        /* GBL_OBJ_* */

@@ -81,7 +81,7 @@ EXPORTED_SYMBOLS = [
     "gbl_objective_create", "gbl_objective_free", "gbl_objective_get_gradients", "gbl_objective_boost_from_score",
     "gbl_objective_is_constant_hessian",
     "gbl_device_malloc", "gbl_device_free", "gbl_memcpy_h2d", "gbl_memcpy_d2h", "gbl_device_fill_f64",
-    "gbl_device_synchronize",
+    "gbl_device_synchronize", "gbl_partition_rows_noalloc",
 ]
 
 _lib = None
@@ -417,6 +417,15 @@ class Learner:
         if self.handle:
             lib().gbl_learner_free(self.handle)
             self.handle = None
+
+
+def partition_rows_noalloc(dataset, feature, threshold_bin, default_left, indices_dev, num_indices, out_indices_dev,
+                           out_left_count_dev, stream=None):
+    """gbl_partition_rows_noalloc: stable split of a row list with library-resident scratch (no allocation)."""
+    check(lib().gbl_partition_rows_noalloc(dataset.handle, ctypes.c_int32(feature), ctypes.c_uint32(threshold_bin),
+                                           ctypes.c_int32(1 if default_left else 0), _dev(indices_dev),
+                                           ctypes.c_int32(num_indices), _dev(out_indices_dev), _dev(out_left_count_dev),
+                                           ctypes.c_void_p(stream) if stream else None))
 
 
 def synchronize(device=0):
