@@ -78,6 +78,12 @@ LGBM_B200_EXPORT int LGBM_NetworkGetNcclUniqueId(uint8_t out_id[128]);
 LGBM_B200_EXPORT int LGBM_NetworkInitWithNccl(const uint8_t id[128], int num_machines, int rank, int device_id);
 /* src/c_api.cpp:2781 */
 LGBM_B200_EXPORT int LGBM_NetworkFree(void);
+/* not in the reference (test tap, runs on the host without a GPU): BinMapper::FindBin (src/io/bin.cpp:313-508) on one
+ * column's sampled non-zero values.  out_scalars = {num_bin, missing_type, default_bin, most_freq_bin, is_trivial};
+ * out_upper_bounds receives num_bin doubles (capacity `cap`). */
+LGBM_B200_EXPORT int LGBM_B200_FindBin(double* values, int num_values, int64_t total_sample_cnt, int max_bin,
+                                       int min_data_in_bin, int min_split_data, int pre_filter, int use_missing,
+                                       int zero_as_missing, int32_t out_scalars[5], double* out_upper_bounds, int cap);
 /* not in the reference: the C-ABI learner handle behind a booster (gbl_learner*), for timers and profiling */
 LGBM_B200_EXPORT int LGBM_BoosterGetLearnerHandle(BoosterHandle handle, void** out_learner);
 /* not in the reference: raw (unconverted) training scores, device -> host */

@@ -20,7 +20,7 @@ LGBM_EXPORTED_SYMBOLS = [
     "LGBM_BoosterNumberOfTotalModel", "LGBM_BoosterGetNumPredict", "LGBM_BoosterGetPredict",
     "LGBM_BoosterPredictForMat", "LGBM_BoosterSaveModelToString", "LGBM_NetworkGetNcclUniqueId",
     "LGBM_NetworkInitWithNccl", "LGBM_NetworkFree", "LGBM_BoosterGetTrainScoreRaw",
-    "LGBM_DatasetCreateFromMatWithSample", "LGBM_BoosterGetLearnerHandle",
+    "LGBM_DatasetCreateFromMatWithSample", "LGBM_BoosterGetLearnerHandle", "LGBM_B200_FindBin",
 ]
 
 _lib = None
@@ -170,6 +170,21 @@ class Booster:
         if self.handle:
             lib().LGBM_BoosterFree(self.handle)
             self.handle = None
+
+
+def find_bin(values, total_sample_cnt, max_bin=255, min_data_in_bin=3, min_split_data=20, pre_filter=True,
+             use_missing=True, zero_as_missing=False):
+    """Host BinMapper::FindBin on one column's sampled non-zero values (no GPU involved)."""
+    v = np.ascontiguousarray(values, dtype=np.float64).copy()
+    sc = (ctypes.c_int32 * 5)()
+    ub = np.zeros(max_bin + 2, dtype=np.float64)
+    _check(lib().LGBM_B200_FindBin(v.ctypes.data_as(ctypes.c_void_p), ctypes.c_int(len(v)), ctypes.c_int64(total_sample_cnt),
+                                   ctypes.c_int(max_bin), ctypes.c_int(min_data_in_bin), ctypes.c_int(min_split_data),
+                                   ctypes.c_int(int(pre_filter)), ctypes.c_int(int(use_missing)),
+                                   ctypes.c_int(int(zero_as_missing)), sc, ub.ctypes.data_as(ctypes.c_void_p),
+                                   ctypes.c_int(len(ub))))
+    return dict(num_bin=sc[0], missing_type=sc[1], default_bin=sc[2], most_freq_bin=sc[3], is_trivial=bool(sc[4]),
+                upper_bounds=ub[:sc[0]].copy())
 
 
 def network_init_nccl(unique_id, num_machines, rank, device_id):

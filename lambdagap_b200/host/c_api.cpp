@@ -153,6 +153,23 @@ int LGBM_BoosterGetPredict(BoosterHandle handle, int data_idx, int64_t* out_len,
   API_END();
 }
 
+int LGBM_B200_FindBin(double* values, int num_values, int64_t total_sample_cnt, int max_bin, int min_data_in_bin,
+                      int min_split_data, int pre_filter, int use_missing, int zero_as_missing, int32_t out_scalars[5],
+                      double* out_upper_bounds, int cap) {
+  API_BEGIN();
+  BinMapper m;
+  m.FindBin(values, num_values, static_cast<size_t>(total_sample_cnt), max_bin, min_data_in_bin, min_split_data,
+            pre_filter != 0, use_missing != 0, zero_as_missing != 0);
+  out_scalars[0] = m.num_bin();
+  out_scalars[1] = static_cast<int>(m.missing_type());
+  out_scalars[2] = static_cast<int>(m.GetDefaultBin());
+  out_scalars[3] = static_cast<int>(m.GetMostFreqBin());
+  out_scalars[4] = m.is_trivial() ? 1 : 0;
+  if (m.num_bin() > cap) Log::Fatal("LGBM_B200_FindBin: %d bins exceed the output capacity %d", m.num_bin(), cap);
+  for (int b = 0; b < m.num_bin(); ++b) out_upper_bounds[b] = m.BinToValue(b);
+  API_END();
+}
+
 int LGBM_BoosterGetLearnerHandle(BoosterHandle handle, void** out_learner) {
   API_BEGIN();
   Booster* b = reinterpret_cast<Booster*>(handle);

@@ -130,3 +130,33 @@ def make_ranking(num_queries, f, seed=0, min_len=2, max_len=60, zero_frac=0.3, m
     qs = np.quantile(s, [0.52, 0.84, 0.97, 0.99][:max_label])
     y = np.searchsorted(qs, s).astype(np.float32)
     return X, y, sizes.astype(np.int32)
+
+
+def load_golden(name):
+    import os
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", name + ".npz")
+    z = np.load(path)
+    meta = z["meta"]
+    ub = z["upper_bounds"]
+    infos, off = [], 0
+    for row in meta:
+        nb = int(row[0])
+        infos.append(dict(num_bin=nb, missing_type=int(row[1]), default_bin=int(row[2]), most_freq_bin=int(row[3]),
+                          real_index=int(row[4]), upper_bounds=ub[off:off + nb].copy()))
+        off += nb
+    trees = []
+    for i, nl in enumerate(z["num_leaves"]):
+        nl = int(nl)
+        t = {"num_leaves": nl}
+        for key in ("split_feature", "decision_type", "left_child", "right_child", "internal_count", "split_gain",
+                    "threshold", "internal_value"):
+            t[key] = z["tree_" + key][i, :nl - 1]
+        for key in ("leaf_count", "leaf_value"):
+            t[key] = z["tree_" + key][i, :nl]
+        trees.append(t)
+    return dict(X=z["X"], y=z["y"], group=z["group"] if len(z["group"]) else None, infos=infos, bins=z["bins"],
+                scores=z["scores"], params=str(z["params"]), kind=str(z["kind"]), iters=int(z["iters"]), trees=trees)
+
+
+def params_to_dict(params):
+    return dict(tok.split("=", 1) for tok in params.split())

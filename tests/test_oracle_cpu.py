@@ -1,0 +1,149 @@
+"""CPU-only tests (`-m "not gpu"`): the oracle's C restatement and the host-side logic against the golden
+fixtures generated from the unmodified reference (tests/golden/make_golden.py), plus the C-ABI export check.
+No GPU compute is called here."""
+import os
+import re
+
+import numpy as np
+import pytest
+
+from lambdagap_b200 import capi, engine
+from oracle import oracle as O
+from tests import helpers as H
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLDEN = ["binary_float", "binary_quant", "regression_l2", "rank_ndcg", "rank_lambdagap_x", "rank_arpk",
+          "rank_ll_ndcg_pp", "rank_precision"]
+
+
+def _oracle_config(p, kind):
+    return O.make_config(num_leaves=int(p.get("num_leaves", 31)), max_depth=int(p.get("max_depth", -1)),
+                         min_data_in_leaf=int(p.get("min_data_in_leaf", 20)),
+                         use_quantized_grad=int(p.get("use_quantized_grad", "false") == "true"),
+                         num_grad_quant_bins=int(p.get("num_grad_quant_bins", 4)),
+                         is_constant_hessian=int(kind == "regression"),
+                         lambda_l1=float(p.get("lambda_l1", 0.0)), lambda_l2=float(p.get("lambda_l2", 0.0)))
+
+
+@pytest.mark.parametrize("name", GOLDEN)
+def test_oracle_reproduces_reference_trees(name):
+    """The C restatement, fed the reference's own bins, grows the reference's trees."""
+    fx = H.load_golden(name)
+    p = H.params_to_dict(fx["params"])
+    cfg = _oracle_config(p, fx["kind"])
+    lr = float(p.get("learning_rate", 0.1))
+    rank = None
+    if fx["kind"] == "rank":
+        rank = O.RankObjective(p["lambdarank_target"], int(p["lambdarank_truncation_level"]), True, 1.0,
+                               float(p.get("lambdagap_weight", 1.0)))
+    objective = {"binary": "binary", "regression": "regression", "rank": "lambdarank"}[fx["kind"]]
+    trees, score = O.boost(list(fx["bins"]), fx["infos"], fx["y"], objective, cfg, fx["iters"], lr, group=fx["group"], rank=rank)
+    assert len(trees) == len(fx["trees"])
+    quant = bool(cfg.use_quantized_grad)
+    for k, ((root, recs, bias), ref) in enumerate(zip(trees, fx["trees"])):
+        ours = H.build_tree({"root_output": root}, _as_records(recs), fx["infos"], cfg.num_leaves)
+        H.assert_tree_matches(ours, ref, shrinkage=lr, bias=bias, rtol=1e-9 if not quant else 1e-12, what="%s tree %d" % (name, k))
+    np.testing.assert_allclose(score, fx["scores"], rtol=1e-9, atol=1e-12)
+
+
+def _as_records(recs):
+    out = []
+    for r in recs:
+        d = dict(r)
+        out.append(d)
+    return out
+
+
+@pytest.mark.parametrize("name", ["binary_float", "regression_l2", "rank_ndcg"])
+def test_host_bin_mapper_matches_reference(name):
+    """BinMapper::FindBin restated in lambdagap_b200/host/bin_mapper.cpp: boundaries bit-exact vs the reference's."""
+    fx = H.load_golden(name)
+    X = fx["X"].astype(np.float64)
+    n = X.shape[0]
+    for info in fx["infos"]:
+        col = X[:, info["real_index"]]
+        vals = col[(np.abs(col) > 1e-35) | np.isnan(col)]
+        got = engine.find_bin(vals, n, max_bin=255, min_data_in_bin=3, min_split_data=20)
+        assert not got["is_trivial"]
+        for key in ("num_bin", "missing_type", "default_bin", "most_freq_bin"):
+            assert got[key] == info[key], key
+        # the bound stored for the NaN bin itself is a placeholder that no code path reads (ValueToBin stops one
+        # bin earlier, a threshold is never the last bin); the reference happens to store 2.0 there, we store NaN
+        real = info["num_bin"] - (1 if info["missing_type"] == 2 else 0)
+        np.testing.assert_array_equal(got["upper_bounds"][:real], info["upper_bounds"][:real])
+        # and ValueToBin through numpy's searchsorted on those bounds reproduces the reference's bins
+        ub = info["upper_bounds"]
+        nb = info["num_bin"] - (1 if info["missing_type"] == 2 else 0)
+        v = np.where(np.isnan(col), 0.0, col)
+        bins = np.minimum(np.searchsorted(ub[:nb - 1], v, side="left"), nb - 1)
+        if info["missing_type"] == 2:
+            bins = np.where(np.isnan(col), info["num_bin"] - 1, bins)
+        np.testing.assert_array_equal(bins.astype(np.uint8), fx["bins"][fx["infos"].index(info)])
+
+
+def test_oracle_histogram_is_plain_accumulation():
+    rng = np.random.default_rng(0)
+    n = 5000
+    col = rng.integers(0, 37, size=n).astype(np.uint8)
+    g = rng.normal(size=n).astype(np.float32)
+    h = rng.uniform(0.1, 1, size=n).astype(np.float32)
+    info = dict(num_bin=37, missing_type=0, default_bin=0, most_freq_bin=5)
+    idx = np.sort(rng.choice(n, size=1700, replace=False)).astype(np.int32)
+    hist = O.histogram_float(col, info, idx, g, h)
+    m = col[idx] != 5
+    eg = np.bincount(col[idx][m], weights=g[idx][m].astype(np.float64), minlength=37)
+    np.testing.assert_allclose(hist[:, 0], eg, rtol=1e-12, atol=1e-12)
+    assert hist[5, 0] == 0 and hist[5, 1] == 0  # the most-frequent bin is reconstructed by FixHistogram, not summed
+
+
+def test_oracle_discretize_matches_formula():
+    rng = np.random.default_rng(1)
+    g = rng.normal(size=1000).astype(np.float32)
+    h = rng.uniform(0, 0.25, size=1000).astype(np.float32)
+    q, gs, hs = O.discretize(g, h, 4, False)
+    q = q.reshape(-1, 2)
+    assert gs == np.abs(g).max().astype(np.float64) / 2 and hs == np.abs(h).max().astype(np.float64) / 4
+    eg = np.trunc(g.astype(np.float64) * (1.0 / gs) + np.where(g >= 0, 0.5, -0.5)).astype(np.int8)
+    np.testing.assert_array_equal(q[:, 1], eg)
+    np.testing.assert_array_equal(q[:, 0], np.trunc(h.astype(np.float64) * (1.0 / hs) + 0.5).astype(np.int8))
+
+
+def _declared(header, macro):
+    text = open(os.path.join(ROOT, "include", header)).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    text = "\n".join(ln for ln in text.split("\n") if not ln.lstrip().startswith("#"))
+    return re.findall(macro + r"[^;(]*?\b(\w+)\s*\(", text)
+
+
+def test_c_abi_library_exports_every_declared_symbol():
+    """Loads liblambdagap_b200.so / liblgbm_b200.so on this GPU-less machine and checks the headers' symbols."""
+    names = _declared("lambdagap_b200.h", "GBL_API")
+    assert len(names) > 40
+    lib = capi.lib()
+    missing = [n for n in names if not hasattr(lib, n)]
+    assert not missing, missing
+    assert sorted(set(names)) == sorted(set(capi.EXPORTED_SYMBOLS)), set(names) ^ set(capi.EXPORTED_SYMBOLS)
+    hnames = _declared("lgbm_b200_c_api.h", "LGBM_B200_EXPORT")
+    hl = engine.lib()
+    missing = [n for n in hnames if not hasattr(hl, n)]
+    assert not missing, missing
+    assert sorted(set(hnames)) == sorted(set(engine.LGBM_EXPORTED_SYMBOLS))
+
+
+def test_no_cpu_fallback_fails_loudly():
+    """Without an sm_100 device every compute entry point must fail with a clear error, never fall back."""
+    if capi.device_count() > 0:
+        pytest.skip("a GPU is present")
+    infos = [dict(num_bin=4, missing_type=0, default_bin=0, most_freq_bin=0, real_index=0)]
+    with pytest.raises(capi.GblError):
+        capi.Dataset.from_bins(infos, [np.zeros(16, dtype=np.uint8)])
+    X = np.random.default_rng(0).normal(size=(100, 3)).astype(np.float32)
+    with pytest.raises(engine.LightGBMError):
+        engine.Dataset(X, (X[:, 0] > 0).astype(np.float32), params="verbose=-1")
+
+
+def test_config_rejects_what_the_learner_does_not_implement():
+    for bad in ("boosting=dart", "linear_tree=true", "feature_fraction=0.5", "max_bin=1023", "device_type=cpu",
+                "monotone_constraints=1,0", "tree_learner=voting"):
+        with pytest.raises(engine.LightGBMError):
+            engine.Dataset(np.zeros((10, 2), dtype=np.float32), np.zeros(10, dtype=np.float32), params=bad + " verbose=-1")
