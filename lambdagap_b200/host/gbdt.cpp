@@ -51,14 +51,10 @@ void GBDT::Init(const Config* config, const Dataset* train_data, ObjectiveFuncti
 double GBDT::BoostFromAverage() {
   // gbdt.cpp:319-343 (single GPU: no Network::GlobalSyncUpByMean)
   if (models_.empty() && !has_init_score_ && objective_function_ != nullptr && config_->boost_from_average) {
-    double init_score = objective_function_->BoostFromScore(0);
-    if (comm_ != nullptr) {
-      // ObtainAutomaticInitialScore: Network::GlobalSyncUpByMean (gbdt.cpp:306-317)
-      int32_t nranks = 1;
-      GblCheck(gbl_comm_info(comm_, &nranks, nullptr));
-      GblCheck(gbl_comm_allreduce_host_f64(comm_, &init_score, 1, 0));
-      init_score /= nranks;
-    }
+    // single GPU: the objective's own value; sharded rows: label sums reduced over ranks first, so that the start
+    // score (and with it every tree) is the one a single GPU would compute on the full data
+    const double init_score = comm_ != nullptr ? objective_function_->BoostFromScoreGlobal(train_data_->metadata(), comm_)
+                                               : objective_function_->BoostFromScore(0);
     if (std::fabs(init_score) > kEpsilon) {
       // ScoreUpdater::AddScore(val): one fill since all scores are still zero
       GblCheck(gbl_device_fill_f64(device_id_, score_dev_, init_score, num_data_));

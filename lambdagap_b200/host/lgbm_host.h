@@ -261,6 +261,9 @@ class ObjectiveFunction {
   // score / gradients / hessians are DEVICE pointers (boosting on the device, cf. src/boosting/gbdt.cpp:849-858)
   void GetGradients(const double* score, score_t* gradients, score_t* hessians, void* stream) const;
   double BoostFromScore(int class_id) const;
+  // with a communicator: label / weight sums are reduced over ranks first (BinaryLogloss::BoostFromScore does
+  // Network::GlobalSyncUpBySum, binary_objective.hpp:157-160), so every rank starts from the global init score
+  double BoostFromScoreGlobal(const Metadata& metadata, gbl_comm* comm) const;
   bool IsConstantHessian() const;
   const char* GetName() const { return name_.c_str(); }
   std::string ToString() const;

@@ -222,6 +222,27 @@ double ObjectiveFunction::BoostFromScore(int /*class_id*/) const {
   return v;
 }
 
+double ObjectiveFunction::BoostFromScoreGlobal(const Metadata& md, gbl_comm* comm) const {
+  if (name_ == "lambdarank") return 0.0;
+  double sums[2] = {0.0, 0.0};  // suml, sumw
+  const size_t n = md.label.size();
+  const bool has_w = !md.weights.empty();
+  for (size_t i = 0; i < n; ++i) {
+    const double w = has_w ? md.weights[i] : 1.0;
+    const double l = name_ == "binary" ? (md.label[i] > 0 ? 1.0 : 0.0) : static_cast<double>(md.label[i]);
+    sums[0] += l * w;
+    sums[1] += w;
+  }
+  GblCheck(gbl_comm_allreduce_host_f64(comm, sums, 2, 0));
+  if (name_ == "binary") {
+    double pavg = sums[0] / sums[1];
+    pavg = std::min(pavg, 1.0 - kEpsilon);
+    pavg = std::max<double>(pavg, kEpsilon);
+    return std::log(pavg / (1.0f - pavg)) / config_.sigmoid;
+  }
+  return sums[0] / sums[1];
+}
+
 bool ObjectiveFunction::IsConstantHessian() const {
   int32_t v = 0;
   GblCheck(gbl_objective_is_constant_hessian(handle_, &v));
