@@ -17,6 +17,8 @@
 //     ATOMS on a low word plus a rare (|v| / 2^32) carry ATOMS on a high word -> exact 64-bit CTA partial sums,
 //     flushed with 64-bit RED atomics.  Sums are order-independent, so histograms are deterministic and
 //     identical for any grid shape or GPU count.
+#include <cstdlib>
+
 #include "kernels.cuh"
 
 namespace gbl {

@@ -11,6 +11,8 @@
 // In mapper-bin terms DenseBin::SplitInner reduces to:  missing rows (zero bin for MissingType::Zero, last bin
 // for MissingType::NaN) follow default_left; every other row goes left iff bin <= threshold (the most-frequent
 // bin is an ordinary bin here).  Index segments ping-pong between two buffers, so no copy-back is needed.
+#include <cstdlib>
+
 #include "kernels.cuh"
 
 namespace gbl {
