@@ -217,6 +217,10 @@ typedef struct gbl_profile {
   int64_t hist_launches; /* histogram kernel launches that had rows to process */
   int64_t hist_rows;     /* sum of leaf rows over those launches */
   int64_t trees;
+  int64_t partition_rows; /* rows moved by DataPartition::Split */
+  int64_t waves;          /* batched rounds (all leaves that may still be needed are split together) */
+  int64_t expansions;     /* nodes split on the device, including speculative ones the final trees do not use */
+  int64_t splits;         /* splits of the final trees */
 } gbl_profile;
 GBL_API int gbl_learner_set_profiling(gbl_learner* learner, int32_t enabled);
 /* CUDA-event stopwatch on the learner's stream (the stream every kernel of this library is launched on):

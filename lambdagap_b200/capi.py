@@ -53,7 +53,9 @@ class TreeResult(ctypes.Structure):
 class Profile(ctypes.Structure):
     _fields_ = [("hist_ms", ctypes.c_double), ("find_ms", ctypes.c_double), ("partition_ms", ctypes.c_double),
                 ("other_ms", ctypes.c_double), ("collective_ms", ctypes.c_double), ("hist_launches", ctypes.c_int64),
-                ("hist_rows", ctypes.c_int64), ("trees", ctypes.c_int64)]
+                ("hist_rows", ctypes.c_int64), ("trees", ctypes.c_int64),
+                ("partition_rows", ctypes.c_int64), ("waves", ctypes.c_int64), ("expansions", ctypes.c_int64),
+                ("splits", ctypes.c_int64)]
 
 
 class ObjectiveConfig(ctypes.Structure):

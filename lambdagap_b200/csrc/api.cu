@@ -5,11 +5,21 @@
 // the extern "C" boundary.
 #include <cstring>
 
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace gbl {
 
 std::atomic<long long> g_kernel_launches{0};
+
+bool debug_sync_enabled() {
+  static const bool on = [] {
+    const char* e = std::getenv("GBL_DEBUG_SYNC");
+    return e != nullptr && e[0] == '1';
+  }();
+  return on;
+}
 static thread_local char g_last_error[1024] = "everything is fine";
 
 void set_last_error(const char* msg) {

@@ -27,6 +27,9 @@ constexpr int kMaxBin = 256;       // bins per feature held by one histogram row
 constexpr int kTile = 32;          // features per tile = lanes per warp
 constexpr int kTailWords = 8;      // int64 words appended to every histogram slot (data-parallel counts)
 constexpr int kNumSM = 148;        // B200
+constexpr int kPartUnit = 2048;    // rows per partition work unit
+constexpr int kHistUnit = 1024;    // rows per histogram work unit
+constexpr int kSegUnit = 4096;     // rows per score-update work unit
 
 // include/LightGBM/meta.h:54-56: const double kEpsilon = 1e-15f; kMinScore = -inf
 #define GBL_KEPS (static_cast<double>(1e-15f))
@@ -38,6 +41,7 @@ struct GblError : public std::runtime_error {
 void set_last_error(const char* msg);
 [[noreturn]] void fatal(const char* fmt, ...);
 extern std::atomic<long long> g_kernel_launches;
+bool debug_sync_enabled();  // GBL_DEBUG_SYNC=1: synchronise after every launch (never inside a graph capture)
 
 #define GBL_CUDA(call)                                                                              \
   do {                                                                                              \
@@ -51,6 +55,7 @@ extern std::atomic<long long> g_kernel_launches;
     kernel<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__);              \
     ::gbl::g_kernel_launches.fetch_add(1, std::memory_order_relaxed);        \
     GBL_CUDA(cudaGetLastError());                                            \
+    if (::gbl::debug_sync_enabled()) GBL_CUDA(cudaStreamSynchronize(stream)); \
   } while (0)
 
 #define GBL_API_BEGIN() try {
@@ -100,14 +105,20 @@ struct BestSplit {
   long long right_ih;
 };
 
-// LeafSplits (src/treelearner/leaf_splits.hpp:22-275) + DataPartition bookkeeping + best_split_per_leaf_
-struct LeafState {
+// One node of the tree under construction.  LeafSplits (src/treelearner/leaf_splits.hpp:22-275) + the
+// DataPartition segment (data_partition.hpp:24-47) + best_split_per_leaf_ of the node while it is a leaf.
+// Nodes are created in pairs when their parent is expanded; ids grow with creation time (parent id < child id).
+struct Node {
   int begin;
   int count;         // local rows
   int global_count;  // rows over all ranks
   int depth;
   int buf;           // which index buffer holds the segment
   int slot;          // histogram slot
+  int parent;        // -1 for the root
+  int left;          // left child id (right child = left + 1); -1 while the node is a leaf of the grown tree
+  int ref_leaf;      // leaf index in the reference's numbering (set by the replay at the end of the tree)
+  int in_tree;       // 1 = this node's split belongs to the final tree (set by the replay)
   int pad0;
   int pad1;
   double sum_g;
@@ -115,26 +126,39 @@ struct LeafState {
   long long ig;
   long long ih;
   double output;  // LeafSplits::weight(), parent_output of the children
+  double bval;    // bottleneck priority: min of best.gain over the path root..node (<= 0 -> never split)
   BestSplit best;
 };
 
-struct TreeState {
-  int num_leaves_cur;
-  int done;          // no further split with positive gain
-  int num_splits;
-  int smaller;       // leaves of the upcoming FindBestSplits round (-1 = none)
-  int larger;
-  int skip_hist;     // BeforeFindBestSplit said no (single GPU shortcut)
-  int do_split;      // select produced a split for this round
-  int split_leaf;
-  int split_feature;
-  unsigned split_threshold;
-  int split_default_left;
-  int split_left_total;  // filled by the partition
-  unsigned scan_done_counter;
-  unsigned part_done_counter;
-  unsigned part_ticket;
+// One node being expanded in the current wave (see learner.cu for the schedule).
+struct Expand {
+  int node;             // node being split
+  int hist_node;        // child whose histogram is built (the smaller one); root wave: the root itself
+  int hist_slot;        // slot that histogram goes to
+  int skip;             // BeforeFindBestSplit said no: children get no histogram / no scan
+  int part_unit_begin;  // first partition work unit of this node (prefix over the wave)
+  int hist_unit_begin;  // first histogram work unit
+  int left_total;       // rows going left (filled by the plan kernel)
   int pad;
+};
+
+struct TreeState {
+  int num_nodes;
+  int num_expanded;
+  int num_slots;
+  int num_cand;       // nodes expanded by the current wave
+  int part_units;     // partition work units of the current wave
+  int hist_units;     // histogram work units of the current wave
+  int scan_jobs;      // (node, feature-set) scan jobs of the current wave: 2 per expanded node, 1 for the root
+  int done;           // no further wave
+  int last_wave;      // the current wave only applies its split (no histogram / scan needed afterwards)
+  int waves;
+  int num_splits;     // splits of the final tree (set by the replay)
+  int num_segments;   // row segments = leaves of the grown tree (>= leaves of the final tree)
+  int seg_units;
+  int error;          // internal consistency failure (reported by train_finish)
+  unsigned scan_done_counter;
+  unsigned pad;
   // float mode fixed-point scales (powers of two): value_fix = value * g_scale ; value = fix * g_inv
   double g_scale, g_inv, h_scale, h_inv;
   // quantized mode (GradientDiscretizer): grad_scale/hess_scale and inverses
@@ -143,6 +167,7 @@ struct TreeState {
   double root_output;
   long long hist_rows_total;  // sum of rows over this tree's histogram launches (algorithmic-bytes accounting)
   long long hist_launches;
+  long long part_rows_total;  // rows moved by this tree's partitions
 };
 
 struct LearnerParams {  // by-value kernel argument

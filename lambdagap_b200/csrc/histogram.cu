@@ -1,4 +1,4 @@
-// histogram.cu -- per-leaf gradient/hessian histogram construction (the dominant kernel).
+// histogram.cu -- gradient/hessian histogram construction for every node of a wave (the dominant kernel).
 //
 // Reference: Dataset::ConstructHistograms (include/LightGBM/dataset.h:735-766, src/io/dataset.cpp:1262-1454)
 //            -> DenseBin::ConstructHistogramInner / ConstructHistogramIntInner (src/io/dense_bin.hpp:99-222):
@@ -17,6 +17,9 @@
 //     ATOMS on a low word plus a rare (|v| / 2^32) carry ATOMS on a high word -> exact 64-bit CTA partial sums,
 //     flushed with 64-bit RED atomics.  Sums are order-independent, so histograms are deterministic and
 //     identical for any grid shape or GPU count.
+//   * one launch serves a whole wave: the rows of all nodes whose histogram is due are cut into units of kHistUnit
+//     rows; every CTA takes a contiguous run of units, accumulates node by node in shared memory and flushes each
+//     node's partial sums to that node's slot.
 #include <cstdlib>
 
 #include "kernels.cuh"
@@ -25,7 +28,6 @@ namespace gbl {
 
 constexpr int kHistThreads = 1024;
 constexpr int kHistWarps = kHistThreads / 32;
-constexpr int kMinChunk = 1024;   // rows per CTA below which fewer CTAs are used
 constexpr int kPlane = kMaxBin * kTile;  // words per smem plane
 
 // Non-returning shared-memory atomic add on a 32-bit shared-window address (SASS: ATOMS.ADD RZ).
@@ -43,83 +45,39 @@ __device__ __forceinline__ unsigned opaque_u32(unsigned v) {
   return v;
 }
 
-struct HistJob {
-  const int* indices;  // nullptr -> identity
-  int begin;
-  int count;
-};
-
-__device__ inline HistJob resolve_job(const LearnerDev& d, const int* explicit_indices, int explicit_count) {
-  HistJob j;
-  if (explicit_count >= 0) {
-    j.indices = explicit_indices;
-    j.begin = 0;
-    j.count = explicit_count;
-    return j;
+// wave entry owning histogram unit u (entries without units own nothing)
+__device__ inline int hist_owner(const Expand* __restrict__ w, int n, int u) {
+  int lo = 0, hi = n;
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (w[mid].hist_unit_begin > u) {
+      hi = mid;
+    } else {
+      lo = mid + 1;
+    }
   }
-  const TreeState& t = *d.ts;
-  if (t.done || t.skip_hist || t.smaller < 0) {
-    j.indices = nullptr;
-    j.begin = 0;
-    j.count = 0;
-    return j;
-  }
-  const LeafState& L = d.leaves[t.smaller];
-  j.indices = d.idx[L.buf];
-  j.begin = L.begin;
-  j.count = L.count;
-  return j;
-}
-
-// Rows per chunk: one chunk per CTA when it fits under the flush cap, otherwise k equal rounds of chunks so that
-// every CTA gets the same number of chunks (no tail wave).
-__device__ inline int chunk_rows(int n, int grid_x, int cap) {
-  int c = (n + grid_x - 1) / grid_x;
-  if (c > cap) {
-    const int k = (c + cap - 1) / cap;
-    c = (n + grid_x * k - 1) / (grid_x * k);
-  }
-  c = max(c, kMinChunk);
-  c = (c + 255) & ~255;
-  return min(c, cap);
+  return lo - 1;
 }
 
 // ------------------------------------------------------------------------------------------ quantized mode
 // smem: int32 hist[256 bins][32 lanes] + per-warp staging of 32 rows {row, packed (grad << 16) + hess}.
 // Hot loop per row and warp: LDS.64 (row info, broadcast) + LDG.U8 (32 bins = one sector) + ATOMS.ADD.
-__global__ void __launch_bounds__(kHistThreads, 1) hist_quant_kernel(LearnerDev d, long long* __restrict__ out,
-                                                                     const int* explicit_indices, int explicit_count,
-                                                                     int flush_cap) {
-  extern __shared__ int sh[];
-  int2* stage_all = reinterpret_cast<int2*>(sh + kPlane);
-  const HistJob job = resolve_job(d, explicit_indices, explicit_count);
-  if (job.count == 0) return;
-  const int tile = blockIdx.y;
-  const int lane = threadIdx.x & 31;
-  const int warp = threadIdx.x >> 5;
-  const int chunk = chunk_rows(job.count, gridDim.x, flush_cap);
-  const int num_chunks = (job.count + chunk - 1) / chunk;
-  if (static_cast<int>(blockIdx.x) >= num_chunks) return;
+struct QuantAcc {
+  static constexpr int kPlanes = 1;
+  static constexpr int kStageBytes = 8;
+  int* sh;
+  int2* st;
+  const uint8_t* rp;
+  unsigned rs, col;
+  const short* gh;
 
-  for (int e = threadIdx.x; e < kPlane; e += kHistThreads) sh[e] = 0;
-  __syncthreads();
-
-  const uint8_t* rp = opaque_ptr(d.row_bins + tile * kTile + lane);
-  const unsigned rs = static_cast<unsigned>(d.row_stride);
-  int2* st = stage_all + warp * 32;
-  const unsigned col = opaque_u32(static_cast<unsigned>(__cvta_generic_to_shared(sh + lane)));
-  const int lanes_used = min(kTile, d.p.num_features - tile * kTile);
-  long long* __restrict__ dst = out + static_cast<long long>(tile) * kPlane;
-
-  for (int c = blockIdx.x; c < num_chunks; c += gridDim.x) {
-    const int c_begin = c * chunk;
-    const int c_end = min(job.count, c_begin + chunk);
-    for (int base = c_begin + warp * 32; base < c_end; base += kHistWarps * 32) {
+  __device__ __forceinline__ void accumulate(const int* __restrict__ indices, int r0, int r1, int warp, int lane) const {
+    for (int base = r0 + warp * 32; base < r1; base += kHistWarps * 32) {
       const int my = base + lane;
       int2 t = make_int2(0, 0);  // padding rows add 0 to bin(row 0)
-      if (my < c_end) {
-        const int r = job.indices != nullptr ? job.indices[job.begin + my] : my;
-        const int q = d.gh_q[r];                           // int16: high byte grad (signed), low byte hess
+      if (my < r1) {
+        const int r = indices != nullptr ? indices[my] : my;
+        const int q = gh[r];                               // int16: high byte grad (signed), low byte hess
         t = make_int2(r, ((q >> 8) << 16) + (q & 0xff));   // packed (grad << 16) + hess
       }
       st[lane] = t;
@@ -139,8 +97,9 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_quant_kernel(LearnerDev 
       }
       __syncwarp();
     }
-    __syncthreads();
-    // flush + re-zero: widen (g16 | h16) to the reference's (g32 | h32) packing
+  }
+  // flush + re-zero: widen (g16 | h16) to the reference's (g32 | h32) packing
+  __device__ __forceinline__ void flush(long long* __restrict__ dst, int lanes_used) const {
     for (int e = threadIdx.x; e < kPlane; e += kHistThreads) {
       const int s = sh[e];
       if (s != 0) {
@@ -152,9 +111,8 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_quant_kernel(LearnerDev 
         }
       }
     }
-    __syncthreads();
   }
-}
+};
 
 // ------------------------------------------------------------------------------------------ float mode
 // smem: 4 planes of int32 [256][32]: g_lo, g_hi, h_lo, h_hi (16-bit limbs of the 2^k fixed-point value, so no
@@ -162,38 +120,22 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_quant_kernel(LearnerDev 
 // Hot loop per row and warp: LDS.128 + LDG.U8 + 4 ATOMS.ADD.
 constexpr int kFloatFlushCap = 65536;
 
-__global__ void __launch_bounds__(kHistThreads, 1) hist_float_kernel(LearnerDev d, long long* __restrict__ out,
-                                                                     const int* explicit_indices, int explicit_count) {
-  extern __shared__ int sh[];
-  int4* stage_all = reinterpret_cast<int4*>(sh + 4 * kPlane);
-  const HistJob job = resolve_job(d, explicit_indices, explicit_count);
-  if (job.count == 0) return;
-  const int tile = blockIdx.y;
-  const int lane = threadIdx.x & 31;
-  const int warp = threadIdx.x >> 5;
-  const int chunk = chunk_rows(job.count, gridDim.x, kFloatFlushCap);
-  const int num_chunks = (job.count + chunk - 1) / chunk;
-  if (static_cast<int>(blockIdx.x) >= num_chunks) return;
+struct FloatAcc {
+  static constexpr int kPlanes = 4;
+  static constexpr int kStageBytes = 16;
+  int* sh;
+  int4* st;
+  const uint8_t* rp;
+  unsigned rs, col;
+  const int2* gh;
 
-  for (int e = threadIdx.x; e < 4 * kPlane; e += kHistThreads) sh[e] = 0;
-  __syncthreads();
-
-  const uint8_t* rp = opaque_ptr(d.row_bins + tile * kTile + lane);
-  const unsigned rs = static_cast<unsigned>(d.row_stride);
-  int4* st = stage_all + warp * 32;
-  const unsigned col = opaque_u32(static_cast<unsigned>(__cvta_generic_to_shared(sh + lane)));
-  const int lanes_used = min(kTile, d.p.num_features - tile * kTile);
-  longlong2* __restrict__ dst = reinterpret_cast<longlong2*>(out) + static_cast<long long>(tile) * kPlane;
-
-  for (int c = blockIdx.x; c < num_chunks; c += gridDim.x) {
-    const int c_begin = c * chunk;
-    const int c_end = min(job.count, c_begin + chunk);
-    for (int base = c_begin + warp * 32; base < c_end; base += kHistWarps * 32) {
+  __device__ __forceinline__ void accumulate(const int* __restrict__ indices, int r0, int r1, int warp, int lane) const {
+    for (int base = r0 + warp * 32; base < r1; base += kHistWarps * 32) {
       const int my = base + lane;
       int4 t = make_int4(0, 0, 0, 0);
-      if (my < c_end) {
-        const int r = job.indices != nullptr ? job.indices[job.begin + my] : my;
-        const int2 v = d.gh_fix[r];
+      if (my < r1) {
+        const int r = indices != nullptr ? indices[my] : my;
+        const int2 v = gh[r];
         t = make_int4(r, v.x, v.y, 0);
       }
       st[lane] = t;
@@ -221,7 +163,9 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_float_kernel(LearnerDev 
       }
       __syncwarp();
     }
-    __syncthreads();
+  }
+  __device__ __forceinline__ void flush(long long* __restrict__ dst_words, int lanes_used) const {
+    longlong2* __restrict__ dst = reinterpret_cast<longlong2*>(dst_words);
     for (int e = threadIdx.x; e < kPlane; e += kHistThreads) {
       const long long g = (static_cast<long long>(sh[e + kPlane]) << 16) + static_cast<long long>(static_cast<unsigned>(sh[e]));
       const long long h =
@@ -235,8 +179,96 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_float_kernel(LearnerDev 
       sh[e + 2 * kPlane] = 0;
       sh[e + 3 * kPlane] = 0;
     }
-    __syncthreads();
   }
+};
+
+// Shared driver.  Tap mode (explicit_count >= 0): the given row list, split evenly over the CTAs of the tile,
+// into `explicit_out`.  Wave mode: this CTA's contiguous share of the wave's work units, node by node.
+template <class Acc>
+__device__ __forceinline__ void hist_drive(const LearnerDev& d, const Acc& acc, long long* __restrict__ explicit_out,
+                                           const int* explicit_indices, int explicit_count, int cap, int entry_words) {
+  const int tile = blockIdx.y;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int lanes_used = min(kTile, d.p.num_features - tile * kTile);
+  const long long tile_off = static_cast<long long>(tile) * kPlane * entry_words;
+  const int gx = gridDim.x, x = blockIdx.x;
+  if (explicit_count >= 0) {
+    int per = (explicit_count + gx - 1) / gx;
+    per = (per + kHistUnit - 1) / kHistUnit * kHistUnit;
+    const long long r0 = static_cast<long long>(x) * per;
+    const int r1 = static_cast<int>(min(static_cast<long long>(explicit_count), r0 + per));
+    for (int p = static_cast<int>(r0); p < r1; p += cap) {
+      acc.accumulate(explicit_indices, p, min(r1, p + cap), warp, lane);
+      __syncthreads();
+      acc.flush(explicit_out + tile_off, lanes_used);
+      __syncthreads();
+    }
+    return;
+  }
+  const TreeState& t = *d.ts;
+  const int U = t.hist_units, C = t.num_cand;
+  const int u0 = static_cast<int>(static_cast<long long>(U) * x / gx);
+  const int u1 = static_cast<int>(static_cast<long long>(U) * (x + 1) / gx);
+  if (u0 >= u1) return;
+  int ci = hist_owner(d.wave, C, u0);
+  int u = u0;
+  while (u < u1) {
+    const Expand w = d.wave[ci];
+    const int next_begin = d.wave[ci + 1].hist_unit_begin;
+    if (next_begin <= u) {  // entry without units
+      ++ci;
+      continue;
+    }
+    const int ue = min(u1, next_begin);
+    const Node& nd = d.nodes[w.hist_node];
+    const int* __restrict__ indices = d.idx[nd.buf] + nd.begin;
+    const int r0 = (u - w.hist_unit_begin) * kHistUnit;
+    const int r1 = min(nd.count, (ue - w.hist_unit_begin) * kHistUnit);
+    long long* __restrict__ dst = d.hist_pool + static_cast<long long>(w.hist_slot) * d.slot_stride + tile_off;
+    for (int p = r0; p < r1; p += cap) {
+      acc.accumulate(indices, p, min(r1, p + cap), warp, lane);
+      __syncthreads();
+      acc.flush(dst, lanes_used);
+      __syncthreads();
+    }
+    u = ue;
+    ++ci;
+  }
+}
+
+__global__ void __launch_bounds__(kHistThreads, 1) hist_quant_kernel(LearnerDev d, long long* __restrict__ out,
+                                                                     const int* explicit_indices, int explicit_count,
+                                                                     int flush_cap) {
+  extern __shared__ int sh[];
+  if (explicit_count < 0 && (d.ts->done || d.ts->hist_units == 0)) return;
+  for (int e = threadIdx.x; e < kPlane; e += kHistThreads) sh[e] = 0;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  QuantAcc acc;
+  acc.sh = sh;
+  acc.st = reinterpret_cast<int2*>(sh + kPlane) + warp * 32;
+  acc.rp = opaque_ptr(d.row_bins + blockIdx.y * kTile + lane);
+  acc.rs = static_cast<unsigned>(d.row_stride);
+  acc.col = opaque_u32(static_cast<unsigned>(__cvta_generic_to_shared(sh + lane)));
+  acc.gh = d.gh_q;
+  hist_drive(d, acc, out, explicit_indices, explicit_count, flush_cap, 1);
+}
+
+__global__ void __launch_bounds__(kHistThreads, 1) hist_float_kernel(LearnerDev d, long long* __restrict__ out,
+                                                                     const int* explicit_indices, int explicit_count) {
+  extern __shared__ int sh[];
+  if (explicit_count < 0 && (d.ts->done || d.ts->hist_units == 0)) return;
+  for (int e = threadIdx.x; e < 4 * kPlane; e += kHistThreads) sh[e] = 0;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  FloatAcc acc;
+  acc.sh = sh;
+  acc.st = reinterpret_cast<int4*>(sh + 4 * kPlane) + warp * 32;
+  acc.rp = opaque_ptr(d.row_bins + blockIdx.y * kTile + lane);
+  acc.rs = static_cast<unsigned>(d.row_stride);
+  acc.col = opaque_u32(static_cast<unsigned>(__cvta_generic_to_shared(sh + lane)));
+  acc.gh = d.gh_fix;
+  hist_drive(d, acc, out, explicit_indices, explicit_count, kFloatFlushCap, 2);
 }
 
 static const int kSmemQ = kPlane * 4 + kHistWarps * 32 * 8;        // 32 KB + 8 KB staging
@@ -247,20 +279,19 @@ void histogram_setup() {
   GBL_CUDA(cudaFuncSetAttribute(hist_quant_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemQ));
 }
 
-void launch_histogram(const LearnerDev& d, int slot, const int* explicit_indices, int explicit_count,
-                      long long* explicit_out, cudaStream_t s) {
-  long long* out = explicit_out != nullptr ? explicit_out : d.hist_pool + static_cast<long long>(slot) * d.slot_stride;
+void launch_histogram(const LearnerDev& d, const int* explicit_indices, int explicit_count, long long* explicit_out,
+                      cudaStream_t s) {
   const int tiles = d.p.num_tiles;
+  const int gx = std::max(1, (kNumSM + tiles - 1) / tiles);
   if (d.p.quantized) {
     // 16-bit halves hold sums of at most flush_cap rows: |g| <= bins/2, h <= bins (gradient_discretizer.cpp:105-127)
     int flush_cap = (65535 / std::max(1, d.p.num_grad_quant_bins)) & ~255;
     flush_cap = std::max(256, std::min(flush_cap, 1 << 20));
-    const int gx = std::max(1, (kNumSM + tiles - 1) / tiles);
-    GBL_LAUNCH(hist_quant_kernel, dim3(gx, tiles), kHistThreads, kSmemQ, s, d, out, explicit_indices, explicit_count,
-               flush_cap);
+    GBL_LAUNCH(hist_quant_kernel, dim3(gx, tiles), kHistThreads, kSmemQ, s, d, explicit_out, explicit_indices,
+               explicit_count, flush_cap);
   } else {
-    const int gx = std::max(1, (kNumSM + tiles - 1) / tiles);
-    GBL_LAUNCH(hist_float_kernel, dim3(gx, tiles), kHistThreads, kSmemF, s, d, out, explicit_indices, explicit_count);
+    GBL_LAUNCH(hist_float_kernel, dim3(gx, tiles), kHistThreads, kSmemF, s, d, explicit_out, explicit_indices,
+               explicit_count);
   }
 }
 

@@ -15,7 +15,10 @@ struct LearnerDev {
   const FeatMeta* meta;
   // per-tree state
   TreeState* ts;
-  LeafState* leaves;
+  Node* nodes;             // [max_nodes]
+  unsigned long long* bkey;   // [max_nodes] bit pattern of Node::bval where positive, else 0 (compact copy for the selection)
+  unsigned char* expanded;    // [max_nodes] 1 once the node has been split
+  Expand* wave;            // [max_cand + 1] nodes expanded by the current wave
   int* idx[2];             // ping-pong index buffers (DataPartition::indices_)
   // gradients
   const float* grad;       // inputs of this tree
@@ -23,18 +26,33 @@ struct LearnerDev {
   int2* gh_fix;            // float mode: fixed-point pair per row
   short* gh_q;             // quantized mode: int8 [hess, grad] pair per row (gradient_discretizer.cpp:124-127)
   // histograms
-  long long* hist_pool;    // [num_leaves slots][slot_stride int64]
+  long long* hist_pool;    // [max_slots][slot_stride int64]
   long long slot_stride;   // int64 words per slot (including kTailWords)
-  unsigned char* splittable;  // [num_leaves slots][num_features]  FeatureHistogram::is_splittable_
+  unsigned char* splittable;  // [max_slots][num_features]  FeatureHistogram::is_splittable_
   const signed char* feature_mask;  // col sampler by-tree mask or nullptr
-  BestSplit* cand;         // [2][num_features] per-feature candidates of the current round
+  BestSplit* cand;         // [2 * max_cand][num_features] per-feature candidates of the current wave
+  unsigned* job_done;      // [2 * max_cand] features finished per scan job
   gbl_split_record* records;  // [num_leaves - 1]
-  int* block_counts;       // partition scratch
-  double* leaf_values;     // [num_leaves] outputs of the last tree (device-resident score update)
+  // partition scratch
+  int* unit_left;          // [max_part_units + 1] rows going left per work unit, then their exclusive prefix
+  unsigned* unit_bits;     // [max_part_units][kPartUnit / 32] go-left flags of every row of the unit
+  // result of the replay
+  double* leaf_values;     // [num_leaves] outputs of the last tree in the reference's leaf numbering
+  int* leaf_node;          // [num_leaves] node of every final leaf
+  int* split_node;         // [num_leaves] node split by the k-th split of the final tree
+  int* seg_node;           // [max_slots] nodes that hold rows (leaves of the grown tree)
+  int* seg_unit_begin;     // [max_slots + 1] prefix of score-update work units
   // stochastic rounding
   const double* rand_g;
   const double* rand_h;
   int rand_start;
+  // capacities
+  int max_nodes;
+  int max_slots;
+  int max_cand;            // nodes per wave
+  int max_expand;          // expansions per tree
+  int spec_limit;          // expansions after which only certain nodes are expanded (one per wave)
+  int max_part_units;
   LearnerParams p;
 };
 
@@ -46,16 +64,19 @@ void launch_scales_and_convert(const LearnerDev& d, cudaStream_t s);
 
 // histogram.cu
 void histogram_setup();
-void launch_histogram(const LearnerDev& d, int slot, const int* explicit_indices, int explicit_count,
-                      long long* explicit_out, cudaStream_t s);
+// wave mode (explicit_count < 0): every node of the current wave; tap mode: the given row list into explicit_out
+void launch_histogram(const LearnerDev& d, const int* explicit_indices, int explicit_count, long long* explicit_out,
+                      cudaStream_t s);
 
 // split.cu
 void launch_root_init(const LearnerDev& d, cudaStream_t s);
-void launch_find_best(const LearnerDev& d, int round, cudaStream_t s);
+// scans the children of the current wave (or the root), reduces, and selects the next wave; `cond` is the
+// conditional handle of the while-node when running inside the CUDA graph (use_cond != 0)
+void launch_find_best(const LearnerDev& d, int is_root, cudaGraphConditionalHandle cond, int use_cond, cudaStream_t s);
+void launch_finalize(const LearnerDev& d, cudaStream_t s);
 
 // partition.cu
-int partition_grid();
-void launch_partition(const LearnerDev& d, int round, cudaStream_t s);
+void launch_partition(const LearnerDev& d, cudaStream_t s);
 void launch_add_score(const LearnerDev& d, const double* leaf_values_dev, double scale, double bias, double* score,
                       cudaStream_t s);
 void launch_leaf_assignment(const LearnerDev& d, int* out, cudaStream_t s);

@@ -7,6 +7,7 @@
 // inside a tree (the reference CUDA learner synchronises twice per split,
 // src/treelearner/cuda/cuda_single_gpu_tree_learner.cpp:246-325).  With GBL_USE_GRAPH=1 (default) the round
 // sequence is captured once into a CUDA graph and replayed per tree.
+#include <algorithm>
 #include <cstdlib>
 #include <cstring>
 #include <vector>
@@ -24,7 +25,17 @@ struct Learner {
   LearnerDev dev{};
   // owned device memory
   TreeState* ts = nullptr;
-  LeafState* leaves = nullptr;
+  Node* nodes = nullptr;
+  unsigned long long* bkey = nullptr;
+  unsigned char* expanded = nullptr;
+  Expand* wave = nullptr;
+  unsigned* job_done = nullptr;
+  int* unit_left = nullptr;
+  unsigned* unit_bits = nullptr;
+  int* leaf_node = nullptr;
+  int* split_node = nullptr;
+  int* seg_node = nullptr;
+  int* seg_unit_begin = nullptr;
   int* idx[2] = {nullptr, nullptr};
   int2* gh_fix = nullptr;
   short* gh_q = nullptr;
@@ -34,7 +45,6 @@ struct Learner {
   signed char* feature_mask = nullptr;
   BestSplit* cand = nullptr;
   gbl_split_record* records = nullptr;
-  int* block_counts = nullptr;
   double* leaf_values = nullptr;
   double* leaf_values_tmp = nullptr;
   double* rand_g = nullptr;
@@ -52,6 +62,7 @@ struct Learner {
   // graph
   bool use_graph = true;
   cudaGraphExec_t graph_exec = nullptr;
+  cudaGraphConditionalHandle graph_cond = 0;
   const float* graph_grad = nullptr;
   const float* graph_hess = nullptr;
   int graph_rand_start = -1;
@@ -66,7 +77,7 @@ struct Learner {
   size_t ev_used = 0;
   gbl_profile prof{};
   cudaEvent_t timer[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
-  long long graph_kernel_nodes = 0;  // kernels inside the captured graph (launch accounting)
+  bool tree_in_graph = false;        // the pending tree runs as a graph replay (launches counted at train_finish)
 };
 
 enum Stage { kStageHist = 0, kStageFind = 1, kStagePart = 2, kStageOther = 3, kStageComm = 4 };
@@ -142,44 +153,101 @@ static void drop_graph(Learner* L) {
 }
 
 static void free_tree_buffers(Learner* L) {
-  cudaFree(L->leaves);
-  cudaFree(L->hist_pool);
-  cudaFree(L->splittable);
-  cudaFree(L->records);
-  cudaFree(L->leaf_values);
-  cudaFree(L->leaf_values_tmp);
+  void* ptrs[] = {L->nodes, L->bkey, L->expanded, L->wave, L->job_done, L->leaf_node, L->split_node, L->seg_node,
+                  L->seg_unit_begin, L->unit_left, L->unit_bits, L->hist_pool, L->splittable, L->cand, L->records,
+                  L->leaf_values, L->leaf_values_tmp};
+  for (void* p : ptrs) cudaFree(p);
   if (L->records_pinned) cudaFreeHost(L->records_pinned);
-  L->leaves = nullptr;
+  L->nodes = nullptr;
+  L->bkey = nullptr;
+  L->expanded = nullptr;
+  L->wave = nullptr;
+  L->job_done = nullptr;
+  L->leaf_node = nullptr;
+  L->split_node = nullptr;
+  L->seg_node = nullptr;
+  L->seg_unit_begin = nullptr;
+  L->unit_left = nullptr;
+  L->unit_bits = nullptr;
   L->hist_pool = nullptr;
   L->splittable = nullptr;
+  L->cand = nullptr;
   L->records = nullptr;
   L->leaf_values = nullptr;
   L->leaf_values_tmp = nullptr;
   L->records_pinned = nullptr;
 }
 
-// (re)allocates everything that depends on the config
+// (re)allocates everything that depends on the config.
+//
+// Capacities.  K = num_leaves - 1 splits make the final tree.  A wave may expand up to K nodes; waves expand
+// speculatively until spec_limit nodes have been expanded, afterwards one certain node per wave (at most K more).
+// Hence max_expand = spec_limit + 2K - 1 expansions, one fresh histogram slot per expansion, two nodes per expansion.
+// spec_limit is 2K unless the histogram pool would not fit the memory budget (GBL_HIST_POOL_MB, default a quarter
+// of the device's free memory), in which case speculation is cut back -- down to none (the reference's own order).
 static void alloc_tree_buffers(Learner* L) {
   const Dataset* ds = L->ds;
   const int nl = L->cfg.num_leaves;
+  const int K = nl - 1;
   const long long entry_words = L->cfg.use_quantized_grad ? 1 : 2;
   const long long slot_stride = static_cast<long long>(ds->num_tiles) * kMaxBin * kTile * entry_words + kTailWords;
-  L->hist_pool_words = static_cast<size_t>(slot_stride) * nl;
-  GBL_CUDA(cudaMalloc(&L->leaves, sizeof(LeafState) * nl));
+  size_t free_b = 0, total_b = 0;
+  GBL_CUDA(cudaMemGetInfo(&free_b, &total_b));
+  long long budget = static_cast<long long>(free_b / 4);
+  if (const char* e = std::getenv("GBL_HIST_POOL_MB")) budget = std::max(1LL, std::atoll(e)) << 20;
+  const long long slot_bytes = slot_stride * 8;
+  long long spec = 2LL * K;
+  if (const char* e = std::getenv("GBL_SPEC_LIMIT")) spec = std::max(0LL, std::min(spec, std::atoll(e)));
+  while (spec > 0 && (spec + 2LL * K) * slot_bytes > budget) spec /= 2;
+  const int max_expand = static_cast<int>(spec > 0 ? spec + 2LL * K - 1 : K);
+  const int max_slots = max_expand + 1;
+  const int max_nodes = 2 * max_expand + 1;
+  const int max_cand = K;
+  const int max_part_units = static_cast<int>(ds->num_data / kPartUnit) + max_cand + 2;
+  L->hist_pool_words = static_cast<size_t>(slot_stride) * max_slots;
+  GBL_CUDA(cudaMalloc(&L->nodes, sizeof(Node) * max_nodes));
+  GBL_CUDA(cudaMalloc(&L->bkey, sizeof(unsigned long long) * max_nodes));
+  GBL_CUDA(cudaMalloc(&L->expanded, max_nodes));
+  GBL_CUDA(cudaMalloc(&L->wave, sizeof(Expand) * (max_cand + 1)));
+  GBL_CUDA(cudaMalloc(&L->job_done, sizeof(unsigned) * 2 * max_cand));
+  GBL_CUDA(cudaMalloc(&L->leaf_node, sizeof(int) * nl));
+  GBL_CUDA(cudaMalloc(&L->split_node, sizeof(int) * nl));
+  GBL_CUDA(cudaMalloc(&L->seg_node, sizeof(int) * max_slots));
+  GBL_CUDA(cudaMalloc(&L->seg_unit_begin, sizeof(int) * (max_slots + 1)));
+  GBL_CUDA(cudaMalloc(&L->unit_left, sizeof(int) * (max_part_units + 1)));
+  GBL_CUDA(cudaMalloc(&L->unit_bits, sizeof(unsigned) * static_cast<size_t>(max_part_units) * (kPartUnit / 32)));
   GBL_CUDA(cudaMalloc(&L->hist_pool, sizeof(long long) * L->hist_pool_words));
-  GBL_CUDA(cudaMalloc(&L->splittable, static_cast<size_t>(nl) * ds->num_features));
+  GBL_CUDA(cudaMalloc(&L->splittable, static_cast<size_t>(max_slots) * ds->num_features));
+  GBL_CUDA(cudaMalloc(&L->cand, sizeof(BestSplit) * 2 * static_cast<size_t>(max_cand) * ds->num_features));
   GBL_CUDA(cudaMalloc(&L->records, sizeof(gbl_split_record) * nl));
   GBL_CUDA(cudaMemset(L->records, 0, sizeof(gbl_split_record) * nl));
   GBL_CUDA(cudaMalloc(&L->leaf_values, sizeof(double) * nl));
   GBL_CUDA(cudaMalloc(&L->leaf_values_tmp, sizeof(double) * nl));
   GBL_CUDA(cudaMallocHost(&L->records_pinned, sizeof(gbl_split_record) * nl));
   LearnerDev& d = L->dev;
-  d.leaves = L->leaves;
+  d.nodes = L->nodes;
+  d.bkey = L->bkey;
+  d.expanded = L->expanded;
+  d.wave = L->wave;
+  d.job_done = L->job_done;
+  d.leaf_node = L->leaf_node;
+  d.split_node = L->split_node;
+  d.seg_node = L->seg_node;
+  d.seg_unit_begin = L->seg_unit_begin;
+  d.unit_left = L->unit_left;
+  d.unit_bits = L->unit_bits;
   d.hist_pool = L->hist_pool;
   d.slot_stride = slot_stride;
   d.splittable = L->splittable;
+  d.cand = L->cand;
   d.records = L->records;
   d.leaf_values = L->leaf_values;
+  d.max_nodes = max_nodes;
+  d.max_slots = max_slots;
+  d.max_cand = max_cand;
+  d.max_expand = max_expand;
+  d.spec_limit = static_cast<int>(spec);
+  d.max_part_units = max_part_units;
   d.p = make_params(L);
 }
 
@@ -206,8 +274,6 @@ static Learner* learner_create(const Dataset* ds, const gbl_learner_config* cfg,
   GBL_CUDA(cudaMalloc(&L->idx[1], sizeof(int) * (n + 32)));
   GBL_CUDA(cudaMalloc(&L->gh_fix, sizeof(int2) * n));
   GBL_CUDA(cudaMalloc(&L->gh_q, sizeof(short) * n));
-  GBL_CUDA(cudaMalloc(&L->cand, sizeof(BestSplit) * 2 * ds->num_features));
-  GBL_CUDA(cudaMalloc(&L->block_counts, sizeof(int) * partition_grid()));
   GBL_CUDA(cudaMallocHost(&L->ts_pinned, sizeof(TreeState)));
   LearnerDev& d = L->dev;
   d.col_bins = ds->col_bins;
@@ -222,8 +288,6 @@ static Learner* learner_create(const Dataset* ds, const gbl_learner_config* cfg,
   d.gh_fix = L->gh_fix;
   d.gh_q = L->gh_q;
   d.feature_mask = nullptr;
-  d.cand = L->cand;
-  d.block_counts = L->block_counts;
   d.rand_g = nullptr;
   d.rand_h = nullptr;
   d.rand_start = 0;
@@ -243,8 +307,6 @@ static void learner_free(Learner* L) {
   cudaFree(L->idx[1]);
   cudaFree(L->gh_fix);
   cudaFree(L->gh_q);
-  cudaFree(L->cand);
-  cudaFree(L->block_counts);
   cudaFree(L->feature_mask);
   cudaFree(L->rand_g);
   cudaFree(L->rand_h);
@@ -261,14 +323,14 @@ static void learner_free(Learner* L) {
   delete L;
 }
 
-// Enqueues one whole tree on `s` (also the body captured into the CUDA graph).
-static void enqueue_tree(Learner* L, cudaStream_t s) {
+// ---- the three parts of a tree.  prologue: root histogram, root scan, first wave selected.  wave: split every
+// node of the wave, histograms of the smaller children, scan of all children, next wave selected.  epilogue: replay.
+static void enqueue_prologue(Learner* L, cudaStream_t s, cudaGraphConditionalHandle cond, int use_cond) {
   const LearnerDev& d = L->dev;
   const bool multi = L->comm != nullptr && L->comm->num_ranks > 1;
-  L->ev_used = 0;
   {
     StageTimer tm(L, s, kStageOther);
-    GBL_CUDA(cudaMemsetAsync(L->hist_pool, 0, sizeof(long long) * L->hist_pool_words, s));
+    GBL_CUDA(cudaMemsetAsync(L->hist_pool, 0, sizeof(long long) * d.slot_stride, s));  // slot 0; later slots: part_scatter
     launch_tree_begin(d, L->bag_indices, L->bag_count, s);
     launch_maxabs(d, s);
   }
@@ -282,31 +344,122 @@ static void enqueue_tree(Learner* L, cudaStream_t s) {
     StageTimer tm(L, s, kStageOther);
     launch_scales_and_convert(d, s);
   }
-  const int rounds = L->cfg.num_leaves - 1;
-  for (int round = 0; round < rounds; ++round) {
-    {
-      StageTimer tm(L, s, kStageHist);
-      launch_histogram(d, round, nullptr, -1, nullptr, s);
-    }
-    if (multi) {
-      // histogram + (smaller, larger) row counts in one all-reduce; replaces Network::ReduceScatter of
-      // data_parallel_tree_learner.cpp:285-297 and the count sync of :457-458
-      StageTimer tm(L, s, kStageComm);
-      comm_allreduce_i64(L->comm, L->hist_pool + static_cast<long long>(round) * d.slot_stride,
-                         static_cast<size_t>(d.slot_stride), RedOp::kSum, s);
-    }
-    {
-      StageTimer tm(L, s, kStageFind);
-      if (round == 0) launch_root_init(d, s);
-      launch_find_best(d, round, s);
-    }
-    {
-      StageTimer tm(L, s, kStagePart);
-      launch_partition(d, round, s);
-    }
+  {
+    StageTimer tm(L, s, kStageHist);
+    launch_histogram(d, nullptr, -1, nullptr, s);
   }
+  if (multi) {
+    StageTimer tm(L, s, kStageComm);
+    comm_allreduce_i64(L->comm, L->hist_pool, static_cast<size_t>(d.slot_stride), RedOp::kSum, s);
+  }
+  {
+    StageTimer tm(L, s, kStageFind);
+    launch_root_init(d, s);
+    launch_find_best(d, 1, cond, use_cond, s);
+  }
+}
+
+// `first_slot` / `num_slots`: the wave's fresh histogram slots (known to the host only in the host-driven loop)
+static void enqueue_wave(Learner* L, cudaStream_t s, cudaGraphConditionalHandle cond, int use_cond, int first_slot,
+                         int num_slots) {
+  const LearnerDev& d = L->dev;
+  const bool multi = L->comm != nullptr && L->comm->num_ranks > 1;
+  {
+    StageTimer tm(L, s, kStagePart);
+    launch_partition(d, s);
+  }
+  {
+    StageTimer tm(L, s, kStageHist);
+    launch_histogram(d, nullptr, -1, nullptr, s);
+  }
+  if (multi && num_slots > 0) {
+    // the wave's histograms + (smaller, larger) row counts in one all-reduce; replaces Network::ReduceScatter of
+    // data_parallel_tree_learner.cpp:285-297 and the count sync of :457-458
+    StageTimer tm(L, s, kStageComm);
+    comm_allreduce_i64(L->comm, L->hist_pool + static_cast<long long>(first_slot) * d.slot_stride,
+                       static_cast<size_t>(d.slot_stride) * num_slots, RedOp::kSum, s);
+  }
+  {
+    StageTimer tm(L, s, kStageFind);
+    launch_find_best(d, 0, cond, use_cond, s);
+  }
+}
+
+static void enqueue_epilogue(Learner* L, cudaStream_t s) {
+  const LearnerDev& d = L->dev;
+  {
+    StageTimer tm(L, s, kStageOther);
+    launch_finalize(d, s);
+  }
+  const int rounds = L->cfg.num_leaves - 1;
   GBL_CUDA(cudaMemcpyAsync(L->records_pinned, L->records, sizeof(gbl_split_record) * rounds, cudaMemcpyDeviceToHost, s));
   GBL_CUDA(cudaMemcpyAsync(L->ts_pinned, L->ts, sizeof(TreeState), cudaMemcpyDeviceToHost, s));
+}
+
+// Host-driven loop (profiling and the data-parallel learner): the host reads the tree state after every wave.
+static void run_tree_host_loop(Learner* L, cudaStream_t s) {
+  L->ev_used = 0;
+  enqueue_prologue(L, s, 0, 0);
+  for (;;) {
+    GBL_CUDA(cudaMemcpyAsync(L->ts_pinned, L->ts, sizeof(TreeState), cudaMemcpyDeviceToHost, s));
+    GBL_CUDA(cudaStreamSynchronize(s));
+    const TreeState& t = *L->ts_pinned;
+    if (t.done) break;
+    if (t.num_cand <= 0 || t.num_cand > L->dev.max_cand || t.num_slots + t.num_cand > L->dev.max_slots)
+      fatal("learner: corrupt wave state (num_cand=%d, num_slots=%d)", t.num_cand, t.num_slots);
+    enqueue_wave(L, s, 0, 0, t.num_slots, t.last_wave ? 0 : t.num_cand);
+  }
+  enqueue_epilogue(L, s);
+}
+
+// One CUDA graph per learner: prologue -> WHILE(conditional node; body = one wave) -> epilogue.  The scan kernel
+// that selects the next wave also sets the loop condition, so a whole tree runs without the host.
+static void build_graph(Learner* L) {
+  cudaStream_t s = L->stream;
+  cudaGraph_t graph = nullptr;
+  GBL_CUDA(cudaGraphCreate(&graph, 0));
+  try {
+    cudaGraphConditionalHandle cond;
+    GBL_CUDA(cudaGraphConditionalHandleCreate(&cond, graph, 0, cudaGraphCondAssignDefault));
+    cudaGraph_t got = nullptr;
+    // prologue
+    GBL_CUDA(cudaStreamBeginCaptureToGraph(s, graph, nullptr, nullptr, 0, cudaStreamCaptureModeThreadLocal));
+    enqueue_prologue(L, s, cond, 1);
+    cudaStreamCaptureStatus st;
+    const cudaGraphNode_t* deps = nullptr;
+    size_t ndeps = 0;
+    GBL_CUDA(cudaStreamGetCaptureInfo_v2(s, &st, nullptr, nullptr, &deps, &ndeps));
+    std::vector<cudaGraphNode_t> tail(deps, deps + ndeps);
+    GBL_CUDA(cudaStreamEndCapture(s, &got));
+    // while node
+    cudaGraphNodeParams cp = {};
+    cp.type = cudaGraphNodeTypeConditional;
+    cp.conditional.handle = cond;
+    cp.conditional.type = cudaGraphCondTypeWhile;
+    cp.conditional.size = 1;
+    cudaGraphNode_t loop = nullptr;
+    GBL_CUDA(cudaGraphAddNode(&loop, graph, tail.data(), tail.size(), &cp));
+    cudaGraph_t body = cp.conditional.phGraph_out[0];
+    GBL_CUDA(cudaStreamBeginCaptureToGraph(s, body, nullptr, nullptr, 0, cudaStreamCaptureModeThreadLocal));
+    enqueue_wave(L, s, cond, 1, 0, 0);
+    GBL_CUDA(cudaStreamEndCapture(s, &got));
+    // epilogue
+    GBL_CUDA(cudaStreamBeginCaptureToGraph(s, graph, &loop, nullptr, 1, cudaStreamCaptureModeThreadLocal));
+    enqueue_epilogue(L, s);
+    GBL_CUDA(cudaStreamEndCapture(s, &got));
+    GBL_CUDA(cudaGraphInstantiate(&L->graph_exec, graph, 0));
+    L->graph_cond = cond;
+  } catch (...) {
+    cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+    cudaStreamIsCapturing(s, &st);
+    if (st != cudaStreamCaptureStatusNone) {
+      cudaGraph_t junk = nullptr;
+      cudaStreamEndCapture(s, &junk);
+    }
+    cudaGraphDestroy(graph);
+    throw;
+  }
+  cudaGraphDestroy(graph);
 }
 
 static void train_async(Learner* L, const float* grad_dev, const float* hess_dev) {
@@ -323,28 +476,15 @@ static void train_async(Learner* L, const float* grad_dev, const float* hess_dev
   d.rand_h = d.rand_g != nullptr ? L->rand_h : nullptr;
   d.rand_start = L->rand_start;
   const bool multi = L->comm != nullptr && L->comm->num_ranks > 1;
-  if (L->use_graph && !multi) {
+  if (L->use_graph && !multi && !L->profiling) {
     const bool stale = L->graph_exec == nullptr || L->graph_grad != grad_dev || L->graph_hess != hess_dev ||
                        L->graph_rand_start != d.rand_start || L->graph_bag != L->bag_indices ||
                        L->graph_bag_count != L->bag_count;
     if (stale) {
       drop_graph(L);
-      cudaGraph_t graph = nullptr;
       const long long launches_before = g_kernel_launches.load();
-      GBL_CUDA(cudaStreamBeginCapture(L->stream, cudaStreamCaptureModeThreadLocal));
-      try {
-        enqueue_tree(L, L->stream);
-      } catch (...) {
-        cudaStreamEndCapture(L->stream, &graph);
-        if (graph) cudaGraphDestroy(graph);
-        throw;
-      }
-      GBL_CUDA(cudaStreamEndCapture(L->stream, &graph));
-      GBL_CUDA(cudaGraphInstantiate(&L->graph_exec, graph, 0));
-      cudaGraphDestroy(graph);
-      // launches "made" during capture only built graph nodes: count them once per replay instead
-      L->graph_kernel_nodes = g_kernel_launches.load() - launches_before;
-      g_kernel_launches.store(launches_before);
+      build_graph(L);
+      g_kernel_launches.store(launches_before);  // launches "made" during capture only built graph nodes
       L->graph_grad = grad_dev;
       L->graph_hess = hess_dev;
       L->graph_rand_start = d.rand_start;
@@ -352,13 +492,19 @@ static void train_async(Learner* L, const float* grad_dev, const float* hess_dev
       L->graph_bag_count = L->bag_count;
     }
     GBL_CUDA(cudaGraphLaunch(L->graph_exec, L->stream));
-    g_kernel_launches.fetch_add(L->graph_kernel_nodes, std::memory_order_relaxed);
+    L->tree_in_graph = true;
   } else {
-    enqueue_tree(L, L->stream);
+    run_tree_host_loop(L, L->stream);
+    L->tree_in_graph = false;
   }
   L->tree_pending = true;
   L->has_tree = true;
 }
+
+// kernels a tree launched, derived from the device's own counters (the graph replays a data-dependent number of
+// waves): prologue (tree_begin, index init, maxabs, scales, convert, histogram, root_init, scan) + 5 per wave +
+// the replay
+static long long kernels_of_tree(const TreeState& t) { return 8 + 5LL * t.waves + 1; }
 
 static void train_finish(Learner* L, gbl_tree_result* result, gbl_split_record* records) {
   if (!L->tree_pending) fatal("gbl_learner_train_finish: no tree in flight");
@@ -368,6 +514,10 @@ static void train_finish(Learner* L, gbl_tree_result* result, gbl_split_record* 
   const TreeState& t = *L->ts_pinned;
   const int ns = t.num_splits;
   if (ns < 0 || ns > L->cfg.num_leaves - 1) fatal("learner: corrupt tree state (num_splits=%d)", ns);
+  if (t.error != 0)
+    fatal("learner: internal error %d while growing the tree (%s)", t.error,
+          t.error == 1 ? "the replay needed a node that was never expanded" : "expansion capacity exhausted");
+  if (L->tree_in_graph) g_kernel_launches.fetch_add(kernels_of_tree(t), std::memory_order_relaxed);
   if (L->profiling) {
     for (size_t i = 0; i + 1 < L->ev_used; i += 2) {
       float ms = 0.f;
@@ -384,6 +534,10 @@ static void train_finish(Learner* L, gbl_tree_result* result, gbl_split_record* 
   }
   L->prof.hist_launches += t.hist_launches;  // counted on the device whether or not stages are timed
   L->prof.hist_rows += t.hist_rows_total;
+  L->prof.partition_rows += t.part_rows_total;
+  L->prof.waves += t.waves;
+  L->prof.expansions += t.num_expanded;
+  L->prof.splits += ns;
   const bool multi = L->comm != nullptr && L->comm->num_ranks > 1;
   if (multi && ns > 0) {
     // global leaf counts of every split (data_parallel_tree_learner.cpp:457-458): one all-reduce per tree
@@ -615,6 +769,15 @@ int gbl_learner_get_leaf_assignment(gbl_learner* learner, int32_t* out_host) {
   GBL_API_END();
 }
 
+// rows of one final leaf: the union of the row segments below it, sorted (the reference's DataPartition keeps the
+// rows of a leaf in ascending order; segments of a speculatively expanded leaf are each ascending)
+static void download_nodes(Learner* L, std::vector<Node>* nodes, TreeState* ts) {
+  GBL_CUDA(cudaStreamSynchronize(L->stream));
+  GBL_CUDA(cudaMemcpy(ts, L->ts, sizeof(TreeState), cudaMemcpyDeviceToHost));
+  nodes->resize(ts->num_nodes);
+  GBL_CUDA(cudaMemcpy(nodes->data(), L->nodes, sizeof(Node) * ts->num_nodes, cudaMemcpyDeviceToHost));
+}
+
 int gbl_learner_get_leaf_indices(gbl_learner* learner, int32_t leaf, int32_t* out_host, int32_t* out_count) {
   GBL_API_BEGIN();
   Learner* L = LEARNER(learner);
@@ -622,15 +785,30 @@ int gbl_learner_get_leaf_indices(gbl_learner* learner, int32_t leaf, int32_t* ou
   if (!L->has_tree) fatal("gbl_learner_get_leaf_indices: no tree trained yet");
   if (leaf < 0 || leaf >= L->cfg.num_leaves) fatal("gbl_learner_get_leaf_indices: leaf out of range");
   DeviceGuard guard(L->ds->device);
-  GBL_CUDA(cudaStreamSynchronize(L->stream));
-  LeafState ls;
-  GBL_CUDA(cudaMemcpy(&ls, L->leaves + leaf, sizeof(LeafState), cudaMemcpyDeviceToHost));
-  *out_count = ls.count;
-  if (out_host != nullptr && ls.count > 0)
-    GBL_CUDA(cudaMemcpy(out_host, L->idx[ls.buf] + ls.begin, sizeof(int) * ls.count, cudaMemcpyDeviceToHost));
+  std::vector<Node> nodes;
+  TreeState ts;
+  download_nodes(L, &nodes, &ts);
+  int total = 0;
+  for (const Node& nd : nodes) {
+    if (nd.left < 0 && nd.ref_leaf == leaf) total += nd.count;
+  }
+  *out_count = leaf <= ts.num_splits ? total : 0;
+  if (out_host != nullptr && leaf <= ts.num_splits && total > 0) {
+    int at = 0, segments = 0;
+    for (const Node& nd : nodes) {
+      if (nd.left < 0 && nd.ref_leaf == leaf && nd.count > 0) {
+        GBL_CUDA(cudaMemcpy(out_host + at, L->idx[nd.buf] + nd.begin, sizeof(int) * nd.count, cudaMemcpyDeviceToHost));
+        at += nd.count;
+        ++segments;
+      }
+    }
+    if (segments > 1) std::sort(out_host, out_host + total);
+  }
   GBL_API_END();
 }
 
+// histogram of one final leaf.  A leaf that was expanded speculatively no longer owns a slot of its own (the larger
+// child took it over): its histogram is the exact integer sum of the segments' histograms below it.
 int gbl_learner_get_histogram(gbl_learner* learner, int32_t leaf, int32_t feature, double* out_host) {
   GBL_API_BEGIN();
   Learner* L = LEARNER(learner);
@@ -639,27 +817,34 @@ int gbl_learner_get_histogram(gbl_learner* learner, int32_t leaf, int32_t featur
   if (leaf < 0 || leaf >= L->cfg.num_leaves || feature < 0 || feature >= L->ds->num_features)
     fatal("gbl_learner_get_histogram: index out of range");
   DeviceGuard guard(L->ds->device);
-  GBL_CUDA(cudaStreamSynchronize(L->stream));
-  LeafState ls;
-  GBL_CUDA(cudaMemcpy(&ls, L->leaves + leaf, sizeof(LeafState), cudaMemcpyDeviceToHost));
+  std::vector<Node> nodes;
   TreeState ts;
-  GBL_CUDA(cudaMemcpy(&ts, L->ts, sizeof(TreeState), cudaMemcpyDeviceToHost));
+  download_nodes(L, &nodes, &ts);
   const long long words = L->dev.slot_stride;
-  std::vector<long long> slot(words);
-  GBL_CUDA(cudaMemcpy(slot.data(), L->hist_pool + static_cast<long long>(ls.slot) * words, sizeof(long long) * words,
-                      cudaMemcpyDeviceToHost));
   const int tile = feature / kTile, fl = feature % kTile;
   const int nb = L->ds->meta_host[feature].num_bin;
-  for (int b = 0; b < nb; ++b) {
-    const long long e = (static_cast<long long>(tile) * kMaxBin + b) * kTile + fl;
-    if (L->cfg.use_quantized_grad) {
-      const long long v = slot[e];
-      out_host[2 * b] = static_cast<double>(static_cast<int>(v >> 32));
-      out_host[2 * b + 1] = static_cast<double>(static_cast<unsigned>(v & 0xffffffffLL));
-    } else {
-      out_host[2 * b] = static_cast<double>(slot[2 * e]) * ts.g_inv;
-      out_host[2 * b + 1] = static_cast<double>(slot[2 * e + 1]) * ts.h_inv;
+  const bool quant = L->cfg.use_quantized_grad != 0;
+  std::vector<long long> slot(words);
+  std::vector<long long> sum_g(nb, 0), sum_h(nb, 0);
+  for (const Node& nd : nodes) {
+    if (!(nd.left < 0 && nd.ref_leaf == leaf)) continue;
+    GBL_CUDA(cudaMemcpy(slot.data(), L->hist_pool + static_cast<long long>(nd.slot) * words, sizeof(long long) * words,
+                        cudaMemcpyDeviceToHost));
+    for (int b = 0; b < nb; ++b) {
+      const long long e = (static_cast<long long>(tile) * kMaxBin + b) * kTile + fl;
+      if (quant) {
+        const long long v = slot[e];
+        sum_g[b] += static_cast<long long>(static_cast<int>(v >> 32));
+        sum_h[b] += static_cast<long long>(static_cast<unsigned>(v & 0xffffffffLL));
+      } else {
+        sum_g[b] += slot[2 * e];
+        sum_h[b] += slot[2 * e + 1];
+      }
     }
+  }
+  for (int b = 0; b < nb; ++b) {
+    out_host[2 * b] = quant ? static_cast<double>(sum_g[b]) : static_cast<double>(sum_g[b]) * ts.g_inv;
+    out_host[2 * b + 1] = quant ? static_cast<double>(sum_h[b]) : static_cast<double>(sum_h[b]) * ts.h_inv;
   }
   GBL_API_END();
 }
@@ -691,7 +876,7 @@ int gbl_learner_construct_histogram(gbl_learner* learner, const int32_t* indices
   if (!L->has_tree) fatal("gbl_learner_construct_histogram: train one tree first (gradients are taken from it)");
   if (num_indices < 0 || num_indices > L->ds->num_data) fatal("gbl_learner_construct_histogram: bad num_indices");
   DeviceGuard guard(L->ds->device);
-  launch_histogram(L->dev, 0, indices_dev, static_cast<int>(num_indices), reinterpret_cast<long long*>(out_hist_dev),
+  launch_histogram(L->dev, indices_dev, static_cast<int>(num_indices), reinterpret_cast<long long*>(out_hist_dev),
                    L->stream);
   GBL_API_END();
 }

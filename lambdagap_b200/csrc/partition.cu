@@ -1,5 +1,5 @@
-// partition.cu -- DataPartition::Split as a stable segmented two-way partition of row indices, the leaf
-// bookkeeping that follows a split, and the per-leaf score update.
+// partition.cu -- DataPartition::Split as a stable segmented two-way partition of row indices for every node of the
+// current wave at once, the node bookkeeping that follows a split, and the per-leaf score update.
 //
 // Reference: DataPartition::Split                 src/treelearner/data_partition.hpp:101-121
 //            ParallelPartitionRunner::Run<false>   include/LightGBM/utils/threading.h:118-185 (stable: left block
@@ -11,17 +11,23 @@
 // In mapper-bin terms DenseBin::SplitInner reduces to:  missing rows (zero bin for MissingType::Zero, last bin
 // for MissingType::NaN) follow default_left; every other row goes left iff bin <= threshold (the most-frequent
 // bin is an ordinary bin here).  Index segments ping-pong between two buffers, so no copy-back is needed.
-#include <cstdlib>
-
+//
+// A wave splits many nodes with three launches.  Work is cut into units of kPartUnit rows of one node:
+//   part_count   : one gather of the split feature's bin per row -> go-left bit per row (kept in HBM, 1 bit/row)
+//                  and the number of left rows per unit;
+//   part_plan    : one CTA: prefix over the units, then per node: child nodes, smaller/larger child, histogram slot,
+//                  BeforeFindBestSplit gates and the histogram work list of the wave;
+//   part_scatter : reads the bits back (no second gather) and writes both children in stable order; also clears the
+//                  wave's fresh histogram slots and hands the parent's is_splittable flags to them.
 #include "kernels.cuh"
 
 namespace gbl {
 
 constexpr int kPartThreads = 256;
-constexpr int kPartGrid = kNumSM * 4;
-constexpr int kPartMinChunk = 2048;
-
-int partition_grid() { return kPartGrid; }
+constexpr int kPartWarps = kPartThreads / 32;
+constexpr int kPartGrid = kNumSM * 8;
+constexpr int kUnitWords = kPartUnit / 32;
+constexpr int kPlanThreads = 1024;
 
 struct SplitRule {
   const uint8_t* col;
@@ -30,258 +36,354 @@ struct SplitRule {
   bool default_left;
 };
 
-__device__ inline SplitRule load_rule(const LearnerDev& d) {
-  const TreeState& t = *d.ts;
-  const FeatMeta m = d.meta[t.split_feature];
+__device__ inline SplitRule load_rule(const LearnerDev& d, const BestSplit& bs) {
+  const FeatMeta m = d.meta[bs.feature];
   SplitRule r;
-  r.col = d.col_bins + static_cast<int64_t>(t.split_feature) * d.col_stride;
-  r.threshold = static_cast<int>(t.split_threshold);
+  r.col = d.col_bins + static_cast<int64_t>(bs.feature) * d.col_stride;
+  r.threshold = static_cast<int>(bs.threshold);
   r.missing_bin = -1;
   if (m.missing_type == GBL_MISSING_ZERO) r.missing_bin = m.default_bin;
   if (m.missing_type == GBL_MISSING_NAN) r.missing_bin = m.num_bin - 1;
-  r.default_left = t.split_default_left != 0;
+  r.default_left = bs.default_left != 0;
   return r;
 }
 
 __device__ inline bool goes_left(const SplitRule& r, int row) {
-  const int bin = r.col[row];
+  const int bin = __ldg(r.col + row);
   return bin == r.missing_bin ? r.default_left : bin <= r.threshold;
 }
 
-__device__ inline int part_chunk(int n) {
-  int c = (n + kPartGrid - 1) / kPartGrid;
-  c = max(c, kPartMinChunk);
-  return (c + kPartThreads - 1) / kPartThreads * kPartThreads;
-}
-
-// pass 1: left count of every CTA's chunk
-__global__ void __launch_bounds__(kPartThreads) part_count_kernel(LearnerDev d) {
-  const TreeState& t = *d.ts;
-  if (t.done || !t.do_split) return;
-  const LeafState& L = d.leaves[t.split_leaf];
-  const int n = L.count;
-  const int chunk = part_chunk(n);
-  const int c_begin = blockIdx.x * chunk;
-  if (c_begin >= n) {
-    if (threadIdx.x == 0) d.block_counts[blockIdx.x] = 0;
-    return;
-  }
-  const int c_end = min(n, c_begin + chunk);
-  const int* __restrict__ src = d.idx[L.buf] + L.begin;
-  const SplitRule rule = load_rule(d);
-  int cnt = 0;
-  for (int i = c_begin + threadIdx.x; i < c_end; i += kPartThreads) cnt += goes_left(rule, src[i]) ? 1 : 0;
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
-  __shared__ int s[kPartThreads / 32];
-  if ((threadIdx.x & 31) == 0) s[threadIdx.x >> 5] = cnt;
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    int tot = 0;
-    for (int w = 0; w < kPartThreads / 32; ++w) tot += s[w];
-    d.block_counts[blockIdx.x] = tot;
-  }
-}
-
-// pass 2: stable scatter + (last CTA) leaf bookkeeping for the next round
-__global__ void __launch_bounds__(kPartThreads) part_scatter_kernel(LearnerDev d, int round) {
-  TreeState& t = *d.ts;
-  if (t.done || !t.do_split) return;
-  __shared__ int s_red[kPartThreads / 32];
-  __shared__ int s_prefix, s_total;
-  __shared__ int s_wl[kPartThreads / 32];
-  __shared__ int s_is_last;
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const LeafState L = d.leaves[t.split_leaf];
-  const int n = L.count;
-  const int chunk = part_chunk(n);
-  // prefix over CTA counts (kPartGrid <= 1024 values)
-  int before = 0, total = 0;
-  for (int b = tid; b < kPartGrid; b += kPartThreads) {
-    const int cval = d.block_counts[b];
-    total += cval;
-    if (b < static_cast<int>(blockIdx.x)) before += cval;
-  }
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    before += __shfl_xor_sync(0xffffffffu, before, o);
-    total += __shfl_xor_sync(0xffffffffu, total, o);
-  }
-  if (lane == 0) s_red[warp] = before;
-  __syncthreads();
-  if (tid == 0) {
-    int v = 0;
-    for (int w = 0; w < kPartThreads / 32; ++w) v += s_red[w];
-    s_prefix = v;
-  }
-  __syncthreads();
-  if (lane == 0) s_red[warp] = total;
-  __syncthreads();
-  if (tid == 0) {
-    int v = 0;
-    for (int w = 0; w < kPartThreads / 32; ++w) v += s_red[w];
-    s_total = v;
-  }
-  __syncthreads();
-  const int left_total = s_total;
-  const int c_begin = blockIdx.x * chunk;
-  if (c_begin < n) {
-    const int c_end = min(n, c_begin + chunk);
-    const int* __restrict__ src = d.idx[L.buf] + L.begin;
-    int* __restrict__ dst = d.idx[L.buf ^ 1] + L.begin;
-    const SplitRule rule = load_rule(d);
-    int left_run = s_prefix;                  // lefts written before this tile
-    int right_run = c_begin - s_prefix;       // rights written before this tile
-    for (int base = c_begin; base < c_end; base += kPartThreads) {
-      const int i = base + tid;
-      int row = 0;
-      bool valid = i < c_end, left = false;
-      if (valid) {
-        row = src[i];
-        left = goes_left(rule, row);
-      }
-      const unsigned bl = __ballot_sync(0xffffffffu, valid && left);
-      const unsigned bv = __ballot_sync(0xffffffffu, valid);
-      if (lane == 0) s_wl[warp] = __popc(bl);
-      __syncthreads();
-      int wl_before = 0, tile_left = 0;
-#pragma unroll
-      for (int w = 0; w < kPartThreads / 32; ++w) {
-        const int cw = s_wl[w];
-        if (w < warp) wl_before += cw;
-        tile_left += cw;
-      }
-      const unsigned lt = (1u << lane) - 1u;
-      if (valid) {
-        if (left) {
-          dst[left_run + wl_before + __popc(bl & lt)] = row;
-        } else {
-          const int rights_before = warp * 32 - wl_before + __popc((bv & ~bl) & lt);
-          dst[left_total + right_run + rights_before] = row;
-        }
-      }
-      const int tile_rows = min(kPartThreads, c_end - base);
-      left_run += tile_left;
-      right_run += tile_rows - tile_left;
-      __syncthreads();
+// wave entry owning partition unit u: the last entry whose first unit is <= u (entries without rows own nothing)
+__device__ inline int part_owner(const Expand* __restrict__ w, int n, int u) {
+  int lo = 0, hi = n;  // first entry with part_unit_begin > u lies in (lo, hi]
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (w[mid].part_unit_begin > u) {
+      hi = mid;
+    } else {
+      lo = mid + 1;
     }
   }
-  // ---- last CTA: SerialTreeLearner::SplitInner bookkeeping (serial_tree_learner.cpp:776-907)
-  __threadfence();
-  __syncthreads();
-  if (tid == 0) {
-    const unsigned prev = atomicAdd(&t.part_done_counter, 1u);
-    s_is_last = (prev == gridDim.x - 1);
+  return lo - 1;
+}
+
+// ------------------------------------------------------------------------------------------------ pass 1
+__global__ void __launch_bounds__(kPartThreads) part_count_kernel(LearnerDev d) {
+  const TreeState& t = *d.ts;
+  if (t.done) return;
+  const int W = t.part_units, C = t.num_cand;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  __shared__ int s_cnt[kPartWarps];
+  for (int u = blockIdx.x; u < W; u += gridDim.x) {
+    const int ci = part_owner(d.wave, C, u);
+    const Expand w = d.wave[ci];
+    const Node& nd = d.nodes[w.node];
+    const int c_begin = (u - w.part_unit_begin) * kPartUnit;
+    const int c_end = min(nd.count, c_begin + kPartUnit);
+    const int* __restrict__ src = d.idx[nd.buf] + nd.begin;
+    const SplitRule rule = load_rule(d, nd.best);
+    unsigned* __restrict__ bits = d.unit_bits + static_cast<size_t>(u) * kUnitWords;
+    int cnt = 0;
+#pragma unroll
+    for (int k = 0; k < kPartUnit / kPartThreads; ++k) {
+      const int i = c_begin + k * kPartThreads + warp * 32 + lane;
+      const bool left = i < c_end && goes_left(rule, src[i]);
+      const unsigned bl = __ballot_sync(0xffffffffu, left);
+      if (lane == 0 && c_begin + k * kPartThreads + warp * 32 < c_end) {
+        bits[k * kPartWarps + warp] = bl;
+        cnt += __popc(bl);
+      }
+    }
+    if (lane == 0) s_cnt[warp] = cnt;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      int tot = 0;
+#pragma unroll
+      for (int x = 0; x < kPartWarps; ++x) tot += s_cnt[x];
+      d.unit_left[u] = tot;
+    }
+    __syncthreads();
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ plan
+// exclusive prefix over the CTA's threads; `carry` accumulates the running total across calls
+__device__ inline int plan_excl_scan(int v, int* s_warp, int& total) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  int x = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int n = __shfl_up_sync(0xffffffffu, x, o);
+    if (lane >= o) x += n;
   }
   __syncthreads();
-  if (!s_is_last) return;
-  __threadfence();
-  const int p = t.split_leaf;
-  const int r = t.num_leaves_cur;
-  const int F = d.p.num_features;
-  const BestSplit bs = L.best;
-  const int nl = left_total, nr = n - left_total;
+  if (lane == 31) s_warp[warp] = x;
+  __syncthreads();
+  int before = 0, tot = 0;
+#pragma unroll
+  for (int k = 0; k < kPlanThreads / 32; ++k) {
+    const int c = s_warp[k];
+    if (k < warp) before += c;
+    tot += c;
+  }
+  total = tot;
+  return before + x - v;
+}
+
+__global__ void __launch_bounds__(kPlanThreads) part_plan_kernel(LearnerDev d) {
+  TreeState& t = *d.ts;
+  if (t.done) return;
+  __shared__ int s_warp[kPlanThreads / 32];
+  __shared__ long long s_hist_rows, s_part_rows;
+  const int tid = threadIdx.x;
+  const int W = t.part_units, C = t.num_cand;
+  const int node_base = t.num_nodes, slot_base = t.num_slots;
   const bool multi = d.p.num_ranks > 1;
-  // smaller / larger: true counts on one GPU (serial_tree_learner.cpp:855); the split's own (rank-invariant)
-  // counts when rows are sharded -- with exact integer histograms the choice does not change any result.
-  const bool left_smaller = multi ? (bs.left_count < bs.right_count) : (nl < nr);
-  const int parent_slot = L.slot;
-  const int new_slot = r;  // == round + 1, fresh
-  // children inherit the parent's is_splittable flags (serial_tree_learner.cpp:394-399)
-  for (int f = tid; f < F; f += kPartThreads) {
-    d.splittable[static_cast<long long>(new_slot) * F + f] = d.splittable[static_cast<long long>(parent_slot) * F + f];
-  }
+  const bool last_wave = t.last_wave != 0;
   if (tid == 0) {
-    LeafState& A = d.leaves[p];
-    LeafState& B = d.leaves[r];
-    B.begin = L.begin + nl;
-    B.count = nr;
-    B.global_count = nr;
-    B.depth = L.depth + 1;
-    B.buf = L.buf ^ 1;
-    B.sum_g = bs.right_sum_g;
-    B.sum_h = bs.right_sum_h;
-    B.ig = bs.right_ig;
-    B.ih = bs.right_ih;
-    B.output = bs.right_output;
-    B.best.gain = -INFINITY;
-    B.best.feature = -1;
-    B.best.real_feature = -1;
+    s_hist_rows = 0;
+    s_part_rows = 0;
+  }
+  // ---- exclusive prefix of the per-unit left counts (in place); unit_left[W] = total
+  int carry = 0;
+  for (int base = 0; base < W; base += kPlanThreads) {
+    const int u = base + tid;
+    const int v = u < W ? d.unit_left[u] : 0;
+    int tot;
+    const int ex = plan_excl_scan(v, s_warp, tot);
+    if (u < W) d.unit_left[u] = carry + ex;
+    carry += tot;
+  }
+  if (tid == 0) d.unit_left[W] = carry;
+  __syncthreads();
+  // ---- children of every expanded node (SerialTreeLearner::SplitInner, serial_tree_learner.cpp:776-907)
+  for (int ci = tid; ci < C; ci += kPlanThreads) {
+    Expand& w = d.wave[ci];
+    Node& P = d.nodes[w.node];
+    const int ub = w.part_unit_begin, ue = d.wave[ci + 1].part_unit_begin;
+    const int nl = d.unit_left[ue] - d.unit_left[ub];
+    const int nr = P.count - nl;
+    const BestSplit bs = P.best;
+    // smaller / larger: true counts on one GPU (serial_tree_learner.cpp:855); the split's own (rank-invariant)
+    // counts when rows are sharded -- with exact integer histograms the choice does not change any result.
+    const bool left_smaller = multi ? (bs.left_count < bs.right_count) : (nl < nr);
+    const int a = node_base + 2 * ci, b = a + 1;
+    const int fresh = slot_base + ci;
+    Node& A = d.nodes[a];
+    Node& B = d.nodes[b];
+    A.begin = P.begin;
     A.count = nl;
     A.global_count = nl;
-    A.depth = L.depth + 1;
-    A.buf = L.buf ^ 1;
     A.sum_g = bs.left_sum_g;
     A.sum_h = bs.left_sum_h;
     A.ig = bs.left_ig;
     A.ih = bs.left_ih;
     A.output = bs.left_output;
-    A.slot = left_smaller ? new_slot : parent_slot;
-    B.slot = left_smaller ? parent_slot : new_slot;
-    d.leaf_values[p] = bs.left_output;
-    d.leaf_values[r] = bs.right_output;
-    gbl_split_record& rec = d.records[t.num_splits];
-    rec.left_count = nl;
-    rec.right_count = nr;
-    t.smaller = left_smaller ? p : r;
-    t.larger = left_smaller ? r : p;
+    A.slot = left_smaller ? fresh : P.slot;
+    B.begin = P.begin + nl;
+    B.count = nr;
+    B.global_count = nr;
+    B.sum_g = bs.right_sum_g;
+    B.sum_h = bs.right_sum_h;
+    B.ig = bs.right_ig;
+    B.ih = bs.right_ih;
+    B.output = bs.right_output;
+    B.slot = left_smaller ? P.slot : fresh;
+    Node* ch[2] = {&A, &B};
+    for (int k = 0; k < 2; ++k) {
+      Node& X = *ch[k];
+      X.depth = P.depth + 1;
+      X.buf = P.buf ^ 1;
+      X.parent = w.node;
+      X.left = -1;
+      X.ref_leaf = -1;
+      X.in_tree = 0;
+      X.bval = -INFINITY;
+      X.best.gain = -INFINITY;
+      X.best.feature = -1;
+      X.best.real_feature = -1;
+    }
+    P.left = a;
+    d.expanded[w.node] = 1;
+    w.left_total = nl;
+    w.hist_node = left_smaller ? a : b;
+    w.hist_slot = fresh;
     const int ns = left_smaller ? nl : nr, ng = left_smaller ? nr : nl;
-    long long* tail = d.hist_pool + static_cast<long long>(new_slot) * d.slot_stride + d.slot_stride - kTailWords;
+    long long* tail = d.hist_pool + static_cast<long long>(fresh) * d.slot_stride + d.slot_stride - kTailWords;
     tail[0] = ns;
     tail[1] = ng;
     // BeforeFindBestSplit shortcut when the global counts are already known (single GPU)
-    int skip = 0;
+    int skip = last_wave ? 1 : 0;
     if (!multi) {
-      if (d.p.max_depth > 0 && A.depth >= d.p.max_depth) skip = 1;
+      if (d.p.max_depth > 0 && P.depth + 1 >= d.p.max_depth) skip = 1;
       if (nl < d.p.min_data_in_leaf * 2 && nr < d.p.min_data_in_leaf * 2) skip = 1;
     }
-    t.skip_hist = skip;
-    if (!skip && r + 1 < d.p.num_leaves) {
-      t.hist_rows_total += ns;
+    w.skip = skip;
+    w.hist_unit_begin = skip ? 0 : (ns + kHistUnit - 1) / kHistUnit;  // unit count, prefixed below
+    if (!skip) atomicAdd(reinterpret_cast<unsigned long long*>(&s_hist_rows), static_cast<unsigned long long>(ns));
+    atomicAdd(reinterpret_cast<unsigned long long*>(&s_part_rows), static_cast<unsigned long long>(P.count));
+  }
+  __syncthreads();
+  // ---- histogram work list: prefix of the unit counts
+  carry = 0;
+  for (int base = 0; base < C; base += kPlanThreads) {
+    const int ci = base + tid;
+    const int v = ci < C ? d.wave[ci].hist_unit_begin : 0;
+    int tot;
+    const int ex = plan_excl_scan(v, s_warp, tot);
+    if (ci < C) d.wave[ci].hist_unit_begin = carry + ex;
+    carry += tot;
+  }
+  if (tid == 0) {
+    d.wave[C].hist_unit_begin = carry;
+    t.hist_units = carry;
+    t.num_nodes = node_base + 2 * C;
+    t.num_slots = slot_base + C;
+    t.num_expanded += C;
+    t.scan_jobs = last_wave ? 0 : 2 * C;
+    t.waves += 1;
+    t.part_rows_total += s_part_rows;
+    if (carry > 0) {
+      t.hist_rows_total += s_hist_rows;
       t.hist_launches += 1;
     }
-    t.split_left_total = nl;
-    t.num_leaves_cur = r + 1;
-    t.num_splits += 1;
-    t.do_split = 0;
-    t.part_done_counter = 0;
   }
-  (void)round;
 }
 
-// score[row] += scale * leaf_value[leaf] + bias for every leaf segment; grid.y = leaf
+// ------------------------------------------------------------------------------------------------ pass 2
+__global__ void __launch_bounds__(kPartThreads) part_scatter_kernel(LearnerDev d) {
+  const TreeState& t = *d.ts;
+  if (t.done) return;
+  const int W = t.part_units, C = t.num_cand;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  __shared__ unsigned s_word[kUnitWords];
+  __shared__ int s_pref[kUnitWords];
+  const unsigned lt = (1u << lane) - 1u;
+  for (int u = blockIdx.x; u < W; u += gridDim.x) {
+    const int ci = part_owner(d.wave, C, u);
+    const Expand w = d.wave[ci];
+    const Node& nd = d.nodes[w.node];
+    const int c_begin = (u - w.part_unit_begin) * kPartUnit;
+    const int c_end = min(nd.count, c_begin + kPartUnit);
+    const int nwords = (c_end - c_begin + 31) >> 5;
+    const int lefts_before = d.unit_left[u] - d.unit_left[w.part_unit_begin];
+    const int* __restrict__ src = d.idx[nd.buf] + nd.begin;
+    int* __restrict__ dst = d.idx[nd.buf ^ 1] + nd.begin;
+    const unsigned* __restrict__ bits = d.unit_bits + static_cast<size_t>(u) * kUnitWords;
+    if (tid < kUnitWords) {  // two warps: exclusive prefix of the words' popcounts
+      const unsigned word = tid < nwords ? bits[tid] : 0u;
+      s_word[tid] = word;
+      const int pc = __popc(word);
+      int x = pc;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int n = __shfl_up_sync(0xffffffffu, x, o);
+        if (lane >= o) x += n;
+      }
+      s_pref[tid] = x - pc;
+    }
+    __syncthreads();
+    // total of the first warp's words, added to the second warp's prefixes on the fly
+    const int first_total = s_pref[31] + __popc(s_word[31]);
+    const int right_base = w.left_total + (c_begin - lefts_before);
+#pragma unroll
+    for (int k = 0; k < kUnitWords / kPartWarps; ++k) {
+      const int wi = k * kPartWarps + warp;
+      const int i = c_begin + wi * 32 + lane;
+      if (wi < nwords && i < c_end) {
+        const int row = src[i];
+        const unsigned word = s_word[wi];
+        const int lb = s_pref[wi] + (wi >= 32 ? first_total : 0) + __popc(word & lt);
+        if ((word >> lane) & 1u) {
+          dst[lefts_before + lb] = row;
+        } else {
+          dst[right_base + (wi * 32 + lane - lb)] = row;
+        }
+      }
+    }
+    __syncthreads();
+  }
+  // ---- fresh histogram slots of the wave start at zero (their tail words were set by the plan kernel), and
+  // children inherit the parent's is_splittable flags (serial_tree_learner.cpp:394-399)
+  if (t.last_wave) return;
+  const long long words_per = d.slot_stride - kTailWords;  // multiple of 8192
+  const long long pairs_per = words_per >> 1;
+  const long long gtid = static_cast<long long>(blockIdx.x) * kPartThreads + tid;
+  const long long gsize = static_cast<long long>(gridDim.x) * kPartThreads;
+  const int slot0 = d.wave[0].hist_slot;
+  for (long long e = gtid; e < pairs_per * C; e += gsize) {
+    const long long s = e / pairs_per, o = e - s * pairs_per;
+    if (d.wave[s].skip) continue;
+    reinterpret_cast<longlong2*>(d.hist_pool + (slot0 + s) * d.slot_stride)[o] = make_longlong2(0, 0);
+  }
+  const int F = d.p.num_features;
+  for (long long e = gtid; e < static_cast<long long>(C) * F; e += gsize) {
+    const int ci = static_cast<int>(e / F), f = static_cast<int>(e - static_cast<long long>(ci) * F);
+    const Expand w = d.wave[ci];
+    const Node& nd = d.nodes[w.node];
+    // the parent's slot (and its flags) stays with the larger child; the fresh slot gets a copy
+    d.splittable[static_cast<long long>(w.hist_slot) * F + f] = d.splittable[static_cast<long long>(nd.slot) * F + f];
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ score update
+// Row segments = leaves of the grown tree (a final leaf that was expanded speculatively is the union of several);
+// work units of kSegUnit rows, prefix in seg_unit_begin (built by the replay).
+__device__ inline int seg_owner(const int* __restrict__ begin, int n, int u) {
+  int lo = 0, hi = n;
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (begin[mid] > u) {
+      hi = mid;
+    } else {
+      lo = mid + 1;
+    }
+  }
+  return lo - 1;
+}
+
+// score[row] += scale * leaf_value[leaf] + bias
 __global__ void __launch_bounds__(256) add_score_kernel(LearnerDev d, const double* __restrict__ leaf_values,
                                                         double scale, double bias, double* __restrict__ score) {
-  const int leaf = blockIdx.y;
-  if (leaf >= d.ts->num_leaves_cur) return;
-  const LeafState& L = d.leaves[leaf];
-  const double v = scale * leaf_values[leaf] + bias;
-  const int* __restrict__ src = d.idx[L.buf] + L.begin;
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < L.count; i += gridDim.x * blockDim.x) score[src[i]] += v;
+  const TreeState& t = *d.ts;
+  const int U = t.seg_units, S = t.num_segments;
+  for (int u = blockIdx.x; u < U; u += gridDim.x) {
+    const int si = seg_owner(d.seg_unit_begin, S, u);
+    const Node& nd = d.nodes[d.seg_node[si]];
+    const double v = scale * leaf_values[nd.ref_leaf] + bias;
+    const int c_begin = (u - d.seg_unit_begin[si]) * kSegUnit;
+    const int c_end = min(nd.count, c_begin + kSegUnit);
+    const int* __restrict__ src = d.idx[nd.buf] + nd.begin;
+    for (int i = c_begin + threadIdx.x; i < c_end; i += 256) score[src[i]] += v;
+  }
 }
 
 __global__ void __launch_bounds__(256) leaf_assign_kernel(LearnerDev d, int* __restrict__ out) {
-  const int leaf = blockIdx.y;
-  if (leaf >= d.ts->num_leaves_cur) return;
-  const LeafState& L = d.leaves[leaf];
-  const int* __restrict__ src = d.idx[L.buf] + L.begin;
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < L.count; i += gridDim.x * blockDim.x) out[src[i]] = leaf;
+  const TreeState& t = *d.ts;
+  const int U = t.seg_units, S = t.num_segments;
+  for (int u = blockIdx.x; u < U; u += gridDim.x) {
+    const int si = seg_owner(d.seg_unit_begin, S, u);
+    const Node& nd = d.nodes[d.seg_node[si]];
+    const int c_begin = (u - d.seg_unit_begin[si]) * kSegUnit;
+    const int c_end = min(nd.count, c_begin + kSegUnit);
+    const int* __restrict__ src = d.idx[nd.buf] + nd.begin;
+    for (int i = c_begin + threadIdx.x; i < c_end; i += 256) out[src[i]] = nd.ref_leaf;
+  }
 }
 
-void launch_partition(const LearnerDev& d, int round, cudaStream_t s) {
+void launch_partition(const LearnerDev& d, cudaStream_t s) {
   GBL_LAUNCH(part_count_kernel, kPartGrid, kPartThreads, 0, s, d);
-  GBL_LAUNCH(part_scatter_kernel, kPartGrid, kPartThreads, 0, s, d, round);
+  GBL_LAUNCH(part_plan_kernel, 1, kPlanThreads, 0, s, d);
+  GBL_LAUNCH(part_scatter_kernel, kPartGrid, kPartThreads, 0, s, d);
 }
 
 void launch_add_score(const LearnerDev& d, const double* leaf_values_dev, double scale, double bias, double* score,
                       cudaStream_t s) {
-  dim3 grid(64, d.p.num_leaves);
-  GBL_LAUNCH(add_score_kernel, grid, 256, 0, s, d, leaf_values_dev, scale, bias, score);
+  GBL_LAUNCH(add_score_kernel, kPartGrid, 256, 0, s, d, leaf_values_dev, scale, bias, score);
 }
 
 void launch_leaf_assignment(const LearnerDev& d, int* out, cudaStream_t s) {
-  dim3 grid(64, d.p.num_leaves);
-  GBL_LAUNCH(leaf_assign_kernel, grid, 256, 0, s, d, out);
+  GBL_LAUNCH(leaf_assign_kernel, kPartGrid, 256, 0, s, d, out);
 }
 
 }  // namespace gbl

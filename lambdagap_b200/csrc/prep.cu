@@ -17,51 +17,74 @@ __global__ void __launch_bounds__(256) copy_int_kernel(int* __restrict__ out, co
   if (i < n) out[i] = in[i];
 }
 
-// One CTA: resets TreeState / LeafState for a new tree (SerialTreeLearner::BeforeTrain,
-// src/treelearner/serial_tree_learner.cpp:288-338).
+// One CTA: resets the tree state for a new tree (SerialTreeLearner::BeforeTrain,
+// src/treelearner/serial_tree_learner.cpp:288-338) and sets the root up as the first wave's histogram job.
 __global__ void __launch_bounds__(256) tree_begin_kernel(LearnerDev d, int root_count) {
   const int tid = threadIdx.x;
   for (int l = tid; l < d.p.num_leaves; l += blockDim.x) {
-    LeafState& L = d.leaves[l];
-    L.begin = 0;
-    L.count = 0;
-    L.global_count = 0;
-    L.depth = 0;
-    L.buf = 0;
-    L.slot = l;
-    L.sum_g = 0.0;
-    L.sum_h = 0.0;
-    L.ig = 0;
-    L.ih = 0;
-    L.output = 0.0;
-    L.best.gain = -INFINITY;  // SplitInfo::Reset (split_info.hpp:132-136)
-    L.best.feature = -1;
-    L.best.real_feature = -1;
     d.leaf_values[l] = 0.0;
+    d.leaf_node[l] = l == 0 ? 0 : -1;
   }
+  for (int n = tid; n < d.max_nodes; n += blockDim.x) {
+    d.bkey[n] = 0ull;
+    d.expanded[n] = 0;
+  }
+  for (int j = tid; j < 2 * d.max_cand; j += blockDim.x) d.job_done[j] = 0u;
   // FeatureHistogram::is_splittable_ of the root slot starts true (feature_histogram.hpp:1356)
   for (int f = tid; f < d.p.num_features; f += blockDim.x) d.splittable[f] = 1;
-  __syncthreads();
   if (tid == 0) {
     TreeState& t = *d.ts;
-    t.num_leaves_cur = 1;
+    t.num_nodes = 1;
+    t.num_expanded = 0;
+    t.num_slots = 1;
+    t.num_cand = 1;  // the root "wave": one histogram job, one scan job
+    t.part_units = 0;
+    t.hist_units = (root_count + kHistUnit - 1) / kHistUnit;
+    t.scan_jobs = 1;
     t.done = 0;
+    t.last_wave = 0;
+    t.waves = 0;
     t.num_splits = 0;
-    t.smaller = 0;
-    t.larger = -1;
-    t.skip_hist = 0;
-    t.do_split = 0;
-    t.split_leaf = -1;
+    t.num_segments = 1;
+    t.seg_units = 0;
+    t.error = 0;
     t.scan_done_counter = 0;
-    t.part_done_counter = 0;
-    t.part_ticket = 0;
     t.max_abs_g = 0.f;
     t.max_abs_h = 0.f;
     t.root_output = 0.0;
     t.hist_rows_total = root_count;
     t.hist_launches = 1;
-    d.leaves[0].count = root_count;
-    d.leaves[0].global_count = root_count;
+    t.part_rows_total = 0;
+    Node& R = d.nodes[0];
+    R.begin = 0;
+    R.count = root_count;
+    R.global_count = root_count;
+    R.depth = 0;
+    R.buf = 0;
+    R.slot = 0;
+    R.parent = -1;
+    R.left = -1;
+    R.ref_leaf = 0;
+    R.in_tree = 0;
+    R.sum_g = 0.0;
+    R.sum_h = 0.0;
+    R.ig = 0;
+    R.ih = 0;
+    R.output = 0.0;
+    R.bval = -INFINITY;
+    R.best.gain = -INFINITY;  // SplitInfo::Reset (split_info.hpp:132-136)
+    R.best.feature = -1;
+    R.best.real_feature = -1;
+    Expand& w = d.wave[0];
+    w.node = 0;
+    w.hist_node = 0;
+    w.hist_slot = 0;
+    w.skip = 0;
+    w.part_unit_begin = 0;
+    w.hist_unit_begin = 0;
+    w.left_total = 0;
+    d.wave[1].hist_unit_begin = t.hist_units;
+    d.wave[1].part_unit_begin = 0;
     // data-parallel: the local root count rides in the tail of slot 0 through the histogram all-reduce
     d.hist_pool[d.slot_stride - kTailWords + 0] = root_count;
     d.hist_pool[d.slot_stride - kTailWords + 1] = 0;
