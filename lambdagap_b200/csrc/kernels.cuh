@@ -73,7 +73,9 @@ void launch_root_init(const LearnerDev& d, cudaStream_t s);
 // scans the children of the current wave (or the root), reduces, and selects the next wave; `cond` is the
 // conditional handle of the while-node when running inside the CUDA graph (use_cond != 0)
 void launch_find_best(const LearnerDev& d, int is_root, cudaGraphConditionalHandle cond, int use_cond, cudaStream_t s);
-void launch_finalize(const LearnerDev& d, cudaStream_t s);
+constexpr size_t kFinalizeSmemMax = 200 * 1024;
+size_t finalize_scratch_bytes(const LearnerDev& d);
+void launch_finalize(const LearnerDev& d, unsigned char* global_scratch, cudaStream_t s);
 
 // partition.cu
 void launch_partition(const LearnerDev& d, cudaStream_t s);

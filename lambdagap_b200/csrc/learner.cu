@@ -36,6 +36,7 @@ struct Learner {
   int* split_node = nullptr;
   int* seg_node = nullptr;
   int* seg_unit_begin = nullptr;
+  unsigned char* replay_scratch = nullptr;  // only for trees too large for the replay's shared memory
   int* idx[2] = {nullptr, nullptr};
   int2* gh_fix = nullptr;
   short* gh_q = nullptr;
@@ -155,7 +156,7 @@ static void drop_graph(Learner* L) {
 static void free_tree_buffers(Learner* L) {
   void* ptrs[] = {L->nodes, L->bkey, L->expanded, L->wave, L->job_done, L->leaf_node, L->split_node, L->seg_node,
                   L->seg_unit_begin, L->unit_left, L->unit_bits, L->hist_pool, L->splittable, L->cand, L->records,
-                  L->leaf_values, L->leaf_values_tmp};
+                  L->leaf_values, L->leaf_values_tmp, L->replay_scratch};
   for (void* p : ptrs) cudaFree(p);
   if (L->records_pinned) cudaFreeHost(L->records_pinned);
   L->nodes = nullptr;
@@ -175,6 +176,7 @@ static void free_tree_buffers(Learner* L) {
   L->records = nullptr;
   L->leaf_values = nullptr;
   L->leaf_values_tmp = nullptr;
+  L->replay_scratch = nullptr;
   L->records_pinned = nullptr;
 }
 
@@ -249,6 +251,7 @@ static void alloc_tree_buffers(Learner* L) {
   d.spec_limit = static_cast<int>(spec);
   d.max_part_units = max_part_units;
   d.p = make_params(L);
+  if (finalize_scratch_bytes(d) > kFinalizeSmemMax) GBL_CUDA(cudaMalloc(&L->replay_scratch, finalize_scratch_bytes(d)));
 }
 
 static Learner* learner_create(const Dataset* ds, const gbl_learner_config* cfg, Comm* comm) {
@@ -389,7 +392,7 @@ static void enqueue_epilogue(Learner* L, cudaStream_t s) {
   const LearnerDev& d = L->dev;
   {
     StageTimer tm(L, s, kStageOther);
-    launch_finalize(d, s);
+    launch_finalize(d, L->replay_scratch, s);
   }
   const int rounds = L->cfg.num_leaves - 1;
   GBL_CUDA(cudaMemcpyAsync(L->records_pinned, L->records, sizeof(gbl_split_record) * rounds, cudaMemcpyDeviceToHost, s));

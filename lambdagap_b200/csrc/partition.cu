@@ -83,11 +83,21 @@ __global__ void __launch_bounds__(kPartThreads) part_count_kernel(LearnerDev d) 
     const int* __restrict__ src = d.idx[nd.buf] + nd.begin;
     const SplitRule rule = load_rule(d, nd.best);
     unsigned* __restrict__ bits = d.unit_bits + static_cast<size_t>(u) * kUnitWords;
+    // all row loads first, then all bin gathers, then the ballots: 8 independent loads in flight per thread
+    constexpr int kIters = kPartUnit / kPartThreads;
+    int rows[kIters];
+    int bins[kIters];
+#pragma unroll
+    for (int k = 0; k < kIters; ++k) {
+      const int i = c_begin + k * kPartThreads + warp * 32 + lane;
+      rows[k] = i < c_end ? src[i] : -1;
+    }
+#pragma unroll
+    for (int k = 0; k < kIters; ++k) bins[k] = rows[k] >= 0 ? static_cast<int>(__ldg(rule.col + rows[k])) : -1;
     int cnt = 0;
 #pragma unroll
-    for (int k = 0; k < kPartUnit / kPartThreads; ++k) {
-      const int i = c_begin + k * kPartThreads + warp * 32 + lane;
-      const bool left = i < c_end && goes_left(rule, src[i]);
+    for (int k = 0; k < kIters; ++k) {
+      const bool left = bins[k] >= 0 && (bins[k] == rule.missing_bin ? rule.default_left : bins[k] <= rule.threshold);
       const unsigned bl = __ballot_sync(0xffffffffu, left);
       if (lane == 0 && c_begin + k * kPartThreads + warp * 32 < c_end) {
         bits[k * kPartWarps + warp] = bl;
