@@ -288,8 +288,8 @@ def main():
     value = args.steps / (ms / 1e3)
 
     # ---- roofline of the dominant kernel (histogram construction): a second pass over the same K steps with
-    # CUDA-event stage timing switched on (external event nodes in the tree graph; they perturb the step time,
-    # which is why `value` above is timed without them)
+    # CUDA-event stage timing switched on (the learner then drives its waves from the host instead of replaying
+    # its CUDA graph, which perturbs the step time -- hence `value` above is timed without it)
     lrn.set_profiling(True)
     lrn.profile(reset=True)
     for _ in range(args.steps):
@@ -319,8 +319,10 @@ def main():
     # gradients / hessians in (H2D), one tree, score update, full score vector out (D2H) -- all inside the timed
     # region; the host-side gradient computation between steps (the caller's objective) is not timed.
     e2e = None
-    if world == 1:
+    if True:
         cparams = cfg["params"].replace("objective=%s" % cfg["objective"], "objective=custom")
+        if world > 1:
+            cparams += " tree_learner=data"  # every rank feeds the gradients of its own row shard
         cb = engine.Booster(ds, cparams + " device_type=cuda verbose=-1 gpu_device_id=%d" % device)
         n = local_rows
         g_pin = torch.empty(n, dtype=torch.float32).pin_memory()
@@ -344,17 +346,49 @@ def main():
         e2e_steps = min(args.steps, 10)
         for it in range(2 + e2e_steps):
             host_objective()
-            capi.synchronize(device)
+            barrier()
             t0 = time.perf_counter()
             cb.update_custom(g_np, h_np)
             engine._check(engine.lib().LGBM_BoosterGetTrainScoreRaw(cb.handle, ctypes.byref(nlen), s_np.ctypes.data_as(ctypes.c_void_p)))
             dt = time.perf_counter() - t0
             if it >= 2:
                 total += dt
-        e2e = {"value": e2e_steps / total, "unit": UNIT, "h2d_bytes_per_step": 8 * n, "d2h_bytes_per_step": 8 * n,
+        if world > 1:  # slowest rank
+            tt = torch.tensor([total], dtype=torch.float64, device="cuda")
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            total = float(tt.item())
+        e2e = {"value": e2e_steps / total, "unit": UNIT, "h2d_bytes_per_step": 8 * n * world, "d2h_bytes_per_step": 8 * n * world,
                "steps": e2e_steps, "api": "LGBM_BoosterUpdateOneIterCustom(host grad, host hess) + LGBM_BoosterGetTrainScoreRaw(host)",
                "ms_per_step": 1e3 * total / e2e_steps}
         cb.free()
+
+    # ---- secondary: the same workload with quantized gradients (the bit-exact mode: int8 gradients, integer
+    # histograms), same timing method; reported beside the headline, not instead of it
+    quant_leg = None
+    if world == 1 and not args.quantized:
+        qb = engine.Booster(ds, params + " use_quantized_grad=true stochastic_rounding=false")
+        ql = qb.learner()
+        for _ in range(args.warmup):
+            qb.update()
+        capi.synchronize(device)
+        ql.timer_record(0)
+        for _ in range(args.steps):
+            qb.update()
+        ql.timer_record(1)
+        qms = ql.timer_elapsed_ms(0, 1)
+        ql.set_profiling(True)
+        ql.profile(reset=True)
+        for _ in range(args.steps):
+            qb.update()
+        qp = ql.profile(reset=True)
+        ql.set_profiling(False)
+        q_alg = qp["hist_rows"] * (F * 1 + 2 + 4) + qp["hist_launches"] * (F * 256 * 8)
+        q_ach = q_alg / (qp["hist_ms"] / 1e3) / 1e9 if qp["hist_ms"] > 0 else 0.0
+        quant_leg = {"params": "use_quantized_grad=true stochastic_rounding=false num_grad_quant_bins=4",
+                     "value": args.steps / (qms / 1e3), "unit": UNIT, "ms_per_step": qms / args.steps,
+                     "roofline": {"kernel": "hist_quant_kernel", "achieved": q_ach, "peak": peak, "unit": "GB/s",
+                                  "frac": q_ach / peak, "avg_launch_us": 1e3 * qp["hist_ms"] / max(1, qp["hist_launches"])}}
+        qb.free()
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -369,7 +403,11 @@ def main():
                           "features": F, "params": cfg["params"], "parallelism": "dp%d" % world,
                           "l2_policy": "inputs larger than L2 (no flush)", "dataset_build_s": round(t_ds, 2),
                           "datagen_s": round(t_gen, 2)},
-               "clocks": clk, "gpu_launches": int(launches), "roofline": roofline, "e2e": e2e, "cpu_baseline": cpu}
+               "clocks": clk, "gpu_launches": int(launches), "roofline": roofline, "e2e": e2e, "cpu_baseline": cpu,
+               "schedule": {"waves_per_tree": prof["waves"] / max(1, prof["trees"]),
+                            "expansions_per_tree": prof["expansions"] / max(1, prof["trees"]),
+                            "splits_per_tree": prof["splits"] / max(1, prof["trees"])},
+               "quantized_mode": quant_leg}
         print(json.dumps(out), flush=True)
     if world > 1:
         dist.barrier()

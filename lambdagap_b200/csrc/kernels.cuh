@@ -53,6 +53,8 @@ struct LearnerDev {
   int max_expand;          // expansions per tree
   int spec_limit;          // expansions after which only certain nodes are expanded (one per wave)
   int max_part_units;
+  int spec_min;            // damped waves still take at least this many ranks beyond the expanded nodes
+  float spec_rho;          // fraction of the remaining split budget whose ranks a damped wave considers (1 = exact rule)
   LearnerParams p;
 };
 

@@ -250,6 +250,10 @@ static void alloc_tree_buffers(Learner* L) {
   d.max_expand = max_expand;
   d.spec_limit = static_cast<int>(spec);
   d.max_part_units = max_part_units;
+  d.spec_rho = 0.2f;  // measured on the Higgs shape: 0.15-0.3 is the flat optimum (fewest expansions without more waves)
+  d.spec_min = 8;
+  if (const char* e = std::getenv("GBL_SPEC_RHO")) d.spec_rho = std::min(1.0f, std::max(0.05f, static_cast<float>(std::atof(e))));
+  if (const char* e = std::getenv("GBL_SPEC_MIN")) d.spec_min = std::max(1, std::atoi(e));
   d.p = make_params(L);
   if (finalize_scratch_bytes(d) > kFinalizeSmemMax) GBL_CUDA(cudaMalloc(&L->replay_scratch, finalize_scratch_bytes(d)));
 }
