@@ -185,6 +185,10 @@ GBL_API int gbl_learner_add_prediction_to_score_dev(gbl_learner* learner, double
                                                     double* score_dev);
 /* test taps */
 /* leaf id of every (local) row after the last tree: DataPartition (src/treelearner/data_partition.hpp) */
+/* leaf outputs of the last tree in the reference's leaf numbering, as the device holds them (before shrinkage); with
+ * quant_train_renew_leaf these are the renewed outputs of GradientDiscretizer::RenewIntGradTreeOutput
+ * (src/treelearner/gradient_discretizer.cpp:209-260), which the split records do not carry */
+GBL_API int gbl_learner_get_leaf_values(gbl_learner* learner, double* out_host, int32_t num_leaves);
 GBL_API int gbl_learner_get_leaf_assignment(gbl_learner* learner, int32_t* out_host);
 /* index segment of one leaf, in partition order (DataPartition::GetIndexOnLeaf) */
 GBL_API int gbl_learner_get_leaf_indices(gbl_learner* learner, int32_t leaf, int32_t* out_host, int32_t* out_count);

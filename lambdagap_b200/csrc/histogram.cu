@@ -69,7 +69,10 @@ struct QuantAcc {
   int2* st;
   const uint8_t* rp;
   unsigned rs, col;
-  const short* gh;
+  uint8_t* ghp;  // record base + gradient offset
+  const LearnerDev* dev;
+  double inv_g, inv_h;
+  bool convert;
 
   __device__ __forceinline__ void accumulate(const int* __restrict__ indices, int r0, int r1, int warp, int lane) const {
     for (int base = r0 + warp * 32; base < r1; base += kHistWarps * 32) {
@@ -77,7 +80,16 @@ struct QuantAcc {
       int2 t = make_int2(0, 0);  // padding rows add 0 to bin(row 0)
       if (my < r1) {
         const int r = indices != nullptr ? indices[my] : my;
-        const int q = gh[r];                               // int16: high byte grad (signed), low byte hess
+        short* rec_gh = reinterpret_cast<short*>(ghp + static_cast<size_t>(static_cast<unsigned>(r)) * rs);
+        int q;  // int16: high byte grad (signed), low byte hess
+        if (convert) {  // root pass: GradientDiscretizer::DiscretizeGradients for this row, kept for the later waves
+          const short packed = discretize_row(*dev, r, inv_g, inv_h);
+          *rec_gh = packed;
+          dev->gh_q[r] = packed;
+          q = packed;
+        } else {
+          q = *rec_gh;
+        }
         t = make_int2(r, ((q >> 8) << 16) + (q & 0xff));   // packed (grad << 16) + hess
       }
       st[lane] = t;
@@ -127,7 +139,11 @@ struct FloatAcc {
   int4* st;
   const uint8_t* rp;
   unsigned rs, col;
-  const int2* gh;
+  uint8_t* ghp;  // record base + gradient offset
+  const float* grad;
+  const float* hess;
+  double g_scale, h_scale;
+  bool convert;
 
   __device__ __forceinline__ void accumulate(const int* __restrict__ indices, int r0, int r1, int warp, int lane) const {
     for (int base = r0 + warp * 32; base < r1; base += kHistWarps * 32) {
@@ -135,7 +151,15 @@ struct FloatAcc {
       int4 t = make_int4(0, 0, 0, 0);
       if (my < r1) {
         const int r = indices != nullptr ? indices[my] : my;
-        const int2 v = gh[r];
+        uint8_t* rec_gh = ghp + static_cast<size_t>(static_cast<unsigned>(r)) * rs;
+        int2 v;
+        if (convert) {  // root pass: float gradients -> fixed point, kept in the row record for the later waves
+          v.x = __double2int_rn(static_cast<double>(grad[r]) * g_scale);
+          v.y = __double2int_rn(static_cast<double>(hess[r]) * h_scale);
+          *reinterpret_cast<int2*>(rec_gh) = v;
+        } else {
+          v = *reinterpret_cast<const int2*>(rec_gh);
+        }
         t = make_int4(r, v.x, v.y, 0);
       }
       st[lane] = t;
@@ -247,10 +271,14 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_quant_kernel(LearnerDev 
   QuantAcc acc;
   acc.sh = sh;
   acc.st = reinterpret_cast<int2*>(sh + kPlane) + warp * 32;
-  acc.rp = opaque_ptr(d.row_bins + blockIdx.y * kTile + lane);
-  acc.rs = static_cast<unsigned>(d.row_stride);
+  acc.rp = opaque_ptr(d.rec + blockIdx.y * kTile + lane);
+  acc.rs = static_cast<unsigned>(d.rec_stride);
   acc.col = opaque_u32(static_cast<unsigned>(__cvta_generic_to_shared(sh + lane)));
-  acc.gh = d.gh_q;
+  acc.ghp = d.rec + d.gh_off;
+  acc.dev = &d;
+  acc.inv_g = d.ts->q_inv_grad_scale;
+  acc.inv_h = d.ts->q_inv_hess_scale;
+  acc.convert = explicit_count < 0 && d.ts->waves == 0;
   hist_drive(d, acc, out, explicit_indices, explicit_count, flush_cap, 1);
 }
 
@@ -264,10 +292,17 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_float_kernel(LearnerDev 
   FloatAcc acc;
   acc.sh = sh;
   acc.st = reinterpret_cast<int4*>(sh + 4 * kPlane) + warp * 32;
-  acc.rp = opaque_ptr(d.row_bins + blockIdx.y * kTile + lane);
-  acc.rs = static_cast<unsigned>(d.row_stride);
+  acc.rp = opaque_ptr(d.rec + blockIdx.y * kTile + lane);
+  acc.rs = static_cast<unsigned>(d.rec_stride);
   acc.col = opaque_u32(static_cast<unsigned>(__cvta_generic_to_shared(sh + lane)));
-  acc.gh = d.gh_fix;
+  acc.ghp = d.rec + d.gh_off;
+  acc.grad = d.grad;
+  acc.hess = d.hess;
+  acc.g_scale = d.ts->g_scale;
+  acc.h_scale = d.ts->h_scale;
+  // the first pass of a tree also converts the gradients (to_fixed: exact power-of-two fixed point, |value| <= 2^30);
+  // with several tiles only tile 0 writes them (the other tiles' CTAs compute the same values)
+  acc.convert = explicit_count < 0 && d.ts->waves == 0;
   hist_drive(d, acc, out, explicit_indices, explicit_count, kFloatFlushCap, 2);
 }
 

@@ -8,9 +8,10 @@ namespace gbl {
 struct LearnerDev {
   // dataset
   const uint8_t* col_bins;
-  const uint8_t* row_bins;
+  uint8_t* rec;            // learner-owned row records: [row][32 bins per tile ...][gradient pair], see learner.cu
   int64_t col_stride;
-  int row_stride;
+  int rec_stride;          // bytes between row records
+  int gh_off;              // byte offset of the gradient pair inside a record
   int num_data;  // local rows
   const FeatMeta* meta;
   // per-tree state
@@ -23,8 +24,7 @@ struct LearnerDev {
   // gradients
   const float* grad;       // inputs of this tree
   const float* hess;
-  int2* gh_fix;            // float mode: fixed-point pair per row
-  short* gh_q;             // quantized mode: int8 [hess, grad] pair per row (gradient_discretizer.cpp:124-127)
+  short* gh_q;             // quantized mode: compact copy of the int8 [hess, grad] pairs (gradient_discretizer.cpp:124-127)
   // histograms
   long long* hist_pool;    // [max_slots][slot_stride int64]
   long long slot_stride;   // int64 words per slot (including kTailWords)
@@ -58,8 +58,30 @@ struct LearnerDev {
   LearnerParams p;
 };
 
+// GradientDiscretizer::DiscretizeGradients for one row (gradient_discretizer.cpp:116-160).  Casts truncate toward
+// zero.  Low byte = hess, high byte = grad (int8 pair read as one int16, dense_bin.hpp:181,196).
+__device__ __forceinline__ short discretize_row(const LearnerDev& d, int i, double inv_g, double inv_h) {
+  const double gradient = static_cast<double>(d.grad[i]);
+  double rg = 0.5, rh = 0.5;
+  if (d.rand_g != nullptr) {
+    const int pos = static_cast<int>((static_cast<long long>(i) + d.rand_start) % d.num_data);
+    rg = d.rand_g[pos];
+    rh = d.rand_h[pos];
+  }
+  const signed char qg = gradient >= 0.0 ? static_cast<signed char>(static_cast<int>(gradient * inv_g + rg))
+                                          : static_cast<signed char>(static_cast<int>(gradient * inv_g - rg));
+  signed char qh;
+  if (d.p.is_constant_hessian) {
+    qh = 1;
+  } else {
+    qh = static_cast<signed char>(static_cast<int>(static_cast<double>(d.hess[i]) * inv_h + rh));
+  }
+  return static_cast<short>((static_cast<int>(qg) << 8) | (static_cast<int>(qh) & 0xff));
+}
+
 // prep.cu
 void launch_iota(int* out, int n, cudaStream_t s);
+void launch_build_records(uint8_t* rec, int rec_stride, const uint8_t* row_bins, int row_stride, int n, cudaStream_t s);
 void launch_tree_begin(const LearnerDev& d, const int* bag_indices, int bag_count, cudaStream_t s);
 void launch_maxabs(const LearnerDev& d, cudaStream_t s);
 void launch_scales_and_convert(const LearnerDev& d, cudaStream_t s);
@@ -78,6 +100,9 @@ void launch_find_best(const LearnerDev& d, int is_root, cudaGraphConditionalHand
 constexpr size_t kFinalizeSmemMax = 200 * 1024;
 size_t finalize_scratch_bytes(const LearnerDev& d);
 void launch_finalize(const LearnerDev& d, unsigned char* global_scratch, cudaStream_t s);
+
+void launch_renew_sums(const LearnerDev& d, double* unit_sums, double* leaf_sums, cudaStream_t s);
+void launch_renew_outputs(const LearnerDev& d, const double* leaf_sums, cudaStream_t s);
 
 // partition.cu
 void launch_partition(const LearnerDev& d, cudaStream_t s);

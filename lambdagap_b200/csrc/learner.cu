@@ -36,9 +36,11 @@ struct Learner {
   int* split_node = nullptr;
   int* seg_node = nullptr;
   int* seg_unit_begin = nullptr;
+  double* renew_sums = nullptr;             // [2 * num_leaves] true gradient sums per leaf (quant_train_renew_leaf)
   unsigned char* replay_scratch = nullptr;  // only for trees too large for the replay's shared memory
   int* idx[2] = {nullptr, nullptr};
-  int2* gh_fix = nullptr;
+  uint8_t* rec = nullptr;  // row records (bins + gradient pair), rebuilt when the gradient format changes
+  bool rec_quant = false;
   short* gh_q = nullptr;
   long long* hist_pool = nullptr;
   size_t hist_pool_words = 0;
@@ -156,7 +158,7 @@ static void drop_graph(Learner* L) {
 static void free_tree_buffers(Learner* L) {
   void* ptrs[] = {L->nodes, L->bkey, L->expanded, L->wave, L->job_done, L->leaf_node, L->split_node, L->seg_node,
                   L->seg_unit_begin, L->unit_left, L->unit_bits, L->hist_pool, L->splittable, L->cand, L->records,
-                  L->leaf_values, L->leaf_values_tmp, L->replay_scratch};
+                  L->leaf_values, L->leaf_values_tmp, L->replay_scratch, L->renew_sums};
   for (void* p : ptrs) cudaFree(p);
   if (L->records_pinned) cudaFreeHost(L->records_pinned);
   L->nodes = nullptr;
@@ -177,7 +179,46 @@ static void free_tree_buffers(Learner* L) {
   L->leaf_values = nullptr;
   L->leaf_values_tmp = nullptr;
   L->replay_scratch = nullptr;
+  L->renew_sums = nullptr;
   L->records_pinned = nullptr;
+}
+
+// Row records.  The histogram kernel gathers, per row, the row's bins and its gradient pair.  DRAM serves 64-byte
+// bursts, so two separate gathers (a 32-byte bin sector here, an 8-byte pair there) cost two bursts per row --
+// measured 181 B of DRAM traffic per row against 40 B algorithmic.  A record keeps both together:
+//   [32 bytes of bins per tile ...][gradient pair]   (float mode: int2 fixed point; quantized: int8 [hess, grad])
+// with the pair tucked into the unused tail of the last tile's sector when it fits (quantized Higgs: one 32-byte
+// record per row), else in one extra sector (float Higgs: 64-byte records = one burst per row).  The records belong
+// to the learner, not the dataset: gradients are per learner, and several learners may share one dataset.
+static void record_layout(int num_features, int num_tiles, bool quant, int* gh_off, int* stride) {
+  const int gh_bytes = quant ? 2 : 8;
+  const int lanes_last = num_features - kTile * (num_tiles - 1);
+  const int inside = kTile * (num_tiles - 1) + static_cast<int>(round_up(lanes_last, gh_bytes));
+  if (inside + gh_bytes <= kTile * num_tiles) {
+    *gh_off = inside;
+    *stride = kTile * num_tiles;
+  } else {
+    *gh_off = kTile * num_tiles;
+    *stride = kTile * num_tiles + 32;
+  }
+}
+
+static void build_records(Learner* L) {
+  const Dataset* ds = L->ds;
+  const bool quant = L->cfg.use_quantized_grad != 0;
+  int gh_off = 0, stride = 0;
+  record_layout(ds->num_features, ds->num_tiles, quant, &gh_off, &stride);
+  if (L->rec != nullptr && L->rec_quant == quant) return;
+  cudaFree(L->rec);
+  L->rec = nullptr;
+  GBL_CUDA(cudaMalloc(&L->rec, static_cast<size_t>(ds->num_data) * stride + 64));
+  GBL_CUDA(cudaMemsetAsync(L->rec, 0, static_cast<size_t>(ds->num_data) * stride + 64, L->stream));
+  launch_build_records(L->rec, stride, ds->row_bins, ds->row_stride, static_cast<int>(ds->num_data), L->stream);
+  GBL_CUDA(cudaStreamSynchronize(L->stream));
+  L->rec_quant = quant;
+  L->dev.rec = L->rec;
+  L->dev.rec_stride = stride;
+  L->dev.gh_off = gh_off;
 }
 
 // (re)allocates everything that depends on the config.
@@ -225,6 +266,7 @@ static void alloc_tree_buffers(Learner* L) {
   GBL_CUDA(cudaMemset(L->records, 0, sizeof(gbl_split_record) * nl));
   GBL_CUDA(cudaMalloc(&L->leaf_values, sizeof(double) * nl));
   GBL_CUDA(cudaMalloc(&L->leaf_values_tmp, sizeof(double) * nl));
+  GBL_CUDA(cudaMalloc(&L->renew_sums, sizeof(double) * 2 * nl));
   GBL_CUDA(cudaMallocHost(&L->records_pinned, sizeof(gbl_split_record) * nl));
   LearnerDev& d = L->dev;
   d.nodes = L->nodes;
@@ -279,26 +321,23 @@ static Learner* learner_create(const Dataset* ds, const gbl_learner_config* cfg,
   GBL_CUDA(cudaMemset(L->ts, 0, sizeof(TreeState)));
   GBL_CUDA(cudaMalloc(&L->idx[0], sizeof(int) * (n + 32)));
   GBL_CUDA(cudaMalloc(&L->idx[1], sizeof(int) * (n + 32)));
-  GBL_CUDA(cudaMalloc(&L->gh_fix, sizeof(int2) * n));
   GBL_CUDA(cudaMalloc(&L->gh_q, sizeof(short) * n));
   GBL_CUDA(cudaMallocHost(&L->ts_pinned, sizeof(TreeState)));
   LearnerDev& d = L->dev;
   d.col_bins = ds->col_bins;
-  d.row_bins = ds->row_bins;
   d.col_stride = ds->col_stride;
-  d.row_stride = ds->row_stride;
   d.num_data = static_cast<int>(ds->num_data);
   d.meta = ds->meta_dev;
   d.ts = L->ts;
   d.idx[0] = L->idx[0];
   d.idx[1] = L->idx[1];
-  d.gh_fix = L->gh_fix;
   d.gh_q = L->gh_q;
   d.feature_mask = nullptr;
   d.rand_g = nullptr;
   d.rand_h = nullptr;
   d.rand_start = 0;
   alloc_tree_buffers(L);
+  build_records(L);
   histogram_setup();
   return L;
 }
@@ -312,7 +351,7 @@ static void learner_free(Learner* L) {
   cudaFree(L->ts);
   cudaFree(L->idx[0]);
   cudaFree(L->idx[1]);
-  cudaFree(L->gh_fix);
+  cudaFree(L->rec);
   cudaFree(L->gh_q);
   cudaFree(L->feature_mask);
   cudaFree(L->rand_g);
@@ -397,6 +436,14 @@ static void enqueue_epilogue(Learner* L, cudaStream_t s) {
   {
     StageTimer tm(L, s, kStageOther);
     launch_finalize(d, L->replay_scratch, s);
+    if (L->cfg.use_quantized_grad && L->cfg.quant_train_renew_leaf) {
+      // GradientDiscretizer::RenewIntGradTreeOutput (serial_tree_learner.cpp:238-241); data-parallel: GlobalSum of
+      // the per-leaf sums (gradient_discretizer.cpp:231)
+      launch_renew_sums(d, reinterpret_cast<double*>(L->unit_bits), L->renew_sums, s);
+      if (L->comm != nullptr && L->comm->num_ranks > 1)
+        comm_allreduce_f64(L->comm, L->renew_sums, 2 * static_cast<size_t>(L->cfg.num_leaves), RedOp::kSum, s);
+      launch_renew_outputs(d, L->renew_sums, s);
+    }
   }
   const int rounds = L->cfg.num_leaves - 1;
   GBL_CUDA(cudaMemcpyAsync(L->records_pinned, L->records, sizeof(gbl_split_record) * rounds, cudaMemcpyDeviceToHost, s));
@@ -509,9 +556,10 @@ static void train_async(Learner* L, const float* grad_dev, const float* hess_dev
 }
 
 // kernels a tree launched, derived from the device's own counters (the graph replays a data-dependent number of
-// waves): prologue (tree_begin, index init, maxabs, scales, convert, histogram, root_init, scan) + 5 per wave +
-// the replay
-static long long kernels_of_tree(const TreeState& t) { return 8 + 5LL * t.waves + 1; }
+// waves): prologue (tree_begin, index init, maxabs, scales, histogram, root_init, scan) + 5 per wave + the replay
+static long long kernels_of_tree(const Learner* L, const TreeState& t) {
+  return 7 + 5LL * t.waves + 1 + ((L->cfg.use_quantized_grad && L->cfg.quant_train_renew_leaf) ? 3 : 0);
+}
 
 static void train_finish(Learner* L, gbl_tree_result* result, gbl_split_record* records) {
   if (!L->tree_pending) fatal("gbl_learner_train_finish: no tree in flight");
@@ -524,7 +572,7 @@ static void train_finish(Learner* L, gbl_tree_result* result, gbl_split_record* 
   if (t.error != 0)
     fatal("learner: internal error %d while growing the tree (%s)", t.error,
           t.error == 1 ? "the replay needed a node that was never expanded" : "expansion capacity exhausted");
-  if (L->tree_in_graph) g_kernel_launches.fetch_add(kernels_of_tree(t), std::memory_order_relaxed);
+  if (L->tree_in_graph) g_kernel_launches.fetch_add(kernels_of_tree(L, t), std::memory_order_relaxed);
   if (L->profiling) {
     for (size_t i = 0; i + 1 < L->ev_used; i += 2) {
       float ms = 0.f;
@@ -614,6 +662,7 @@ int gbl_learner_reset_config(gbl_learner* learner, const gbl_learner_config* con
   if (realloc) {
     free_tree_buffers(L);
     alloc_tree_buffers(L);
+    build_records(L);
     L->has_tree = false;
   } else {
     L->dev.p = make_params(L);
@@ -756,6 +805,18 @@ int gbl_learner_add_prediction_to_score_dev(gbl_learner* learner, double shrinka
   if (!L->has_tree) fatal("gbl_learner_add_prediction_to_score_dev: no tree trained yet");
   DeviceGuard guard(L->ds->device);
   launch_add_score(L->dev, L->leaf_values, shrinkage, bias, score_dev, L->stream);
+  GBL_API_END();
+}
+
+int gbl_learner_get_leaf_values(gbl_learner* learner, double* out_host, int32_t num_leaves) {
+  GBL_API_BEGIN();
+  Learner* L = LEARNER(learner);
+  if (L == nullptr || out_host == nullptr) fatal("gbl_learner_get_leaf_values: null argument");
+  if (!L->has_tree) fatal("gbl_learner_get_leaf_values: no tree trained yet");
+  if (num_leaves < 1 || num_leaves > L->cfg.num_leaves) fatal("gbl_learner_get_leaf_values: bad num_leaves");
+  DeviceGuard guard(L->ds->device);
+  GBL_CUDA(cudaStreamSynchronize(L->stream));
+  GBL_CUDA(cudaMemcpy(out_host, L->leaf_values, sizeof(double) * num_leaves, cudaMemcpyDeviceToHost));
   GBL_API_END();
 }
 

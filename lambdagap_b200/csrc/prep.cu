@@ -145,40 +145,22 @@ __global__ void scales_kernel(LearnerDev d) {
   }
 }
 
-// float mode: exact power-of-two fixed point, |value| <= 2^30
-__global__ void __launch_bounds__(256) to_fixed_kernel(LearnerDev d) {
-  const double gs = d.ts->g_scale, hs = d.ts->h_scale;
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < d.num_data; i += gridDim.x * blockDim.x) {
-    int2 v;
-    v.x = __double2int_rn(static_cast<double>(d.grad[i]) * gs);
-    v.y = __double2int_rn(static_cast<double>(d.hess[i]) * hs);
-    d.gh_fix[i] = v;
+// copies the dataset's row-major bin mirror into the learner's row records (16 bytes per thread)
+__global__ void __launch_bounds__(256) build_records_kernel(uint8_t* __restrict__ rec, int rec_stride,
+                                                            const uint8_t* __restrict__ row_bins, int row_stride, int n) {
+  const int per_row = row_stride / 16;
+  const long long total = static_cast<long long>(n) * per_row;
+  for (long long e = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; e < total;
+       e += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long r = e / per_row;
+    const int c = static_cast<int>(e - r * per_row);
+    const uint4 v = *reinterpret_cast<const uint4*>(row_bins + r * row_stride + c * 16);
+    *reinterpret_cast<uint4*>(rec + r * rec_stride + c * 16) = v;
   }
 }
 
-// GradientDiscretizer::DiscretizeGradients, gradient_discretizer.cpp:116-160.  Casts truncate toward zero.
-__global__ void __launch_bounds__(256) discretize_kernel(LearnerDev d) {
-  const double ig = d.ts->q_inv_grad_scale, ih = d.ts->q_inv_hess_scale;
-  const int n = d.num_data;
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-    const double gradient = static_cast<double>(d.grad[i]);
-    double rg = 0.5, rh = 0.5;
-    if (d.rand_g != nullptr) {
-      const int pos = static_cast<int>((static_cast<long long>(i) + d.rand_start) % n);
-      rg = d.rand_g[pos];
-      rh = d.rand_h[pos];
-    }
-    const signed char qg = gradient >= 0.0 ? static_cast<signed char>(static_cast<int>(gradient * ig + rg))
-                                            : static_cast<signed char>(static_cast<int>(gradient * ig - rg));
-    signed char qh;
-    if (d.p.is_constant_hessian) {
-      qh = 1;
-    } else {
-      qh = static_cast<signed char>(static_cast<int>(static_cast<double>(d.hess[i]) * ih + rh));
-    }
-    // low byte = hess, high byte = grad (int8 pair read as one int16, dense_bin.hpp:181,196)
-    d.gh_q[i] = static_cast<short>((static_cast<int>(qg) << 8) | (static_cast<int>(qh) & 0xff));
-  }
+void launch_build_records(uint8_t* rec, int rec_stride, const uint8_t* row_bins, int row_stride, int n, cudaStream_t s) {
+  GBL_LAUNCH(build_records_kernel, kNumSM * 16, 256, 0, s, rec, rec_stride, row_bins, row_stride, n);
 }
 
 void launch_iota(int* out, int n, cudaStream_t s) {
@@ -200,14 +182,10 @@ void launch_maxabs(const LearnerDev& d, cudaStream_t s) {
   GBL_LAUNCH(maxabs_kernel, grid, 256, 0, s, d.grad, d.hess, d.num_data, d.ts);
 }
 
+// scales only: the conversion itself (float mode: to fixed point; quantized: DiscretizeGradients) happens inside the
+// root histogram pass, which reads every row anyway (histogram.cu)
 void launch_scales_and_convert(const LearnerDev& d, cudaStream_t s) {
   GBL_LAUNCH(scales_kernel, 1, 1, 0, s, d);
-  const int grid = std::min((d.num_data + 255) / 256, kNumSM * 8);
-  if (d.p.quantized) {
-    GBL_LAUNCH(discretize_kernel, grid, 256, 0, s, d);
-  } else {
-    GBL_LAUNCH(to_fixed_kernel, grid, 256, 0, s, d);
-  }
 }
 
 }  // namespace gbl

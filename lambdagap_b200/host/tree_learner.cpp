@@ -148,6 +148,12 @@ Tree* B200TreeLearner::FinishTrain() {
                 r.left_output, r.right_output, r.left_count, r.right_count, r.left_sum_hessian, r.right_sum_hessian,
                 static_cast<float>(r.gain + config_->min_gain_to_split), m->missing_type(), r.default_left != 0);
   }
+  if (config_->use_quantized_grad && config_->quant_train_renew_leaf && res.num_splits > 0) {
+    // serial_tree_learner.cpp:238-241: the device recomputed every leaf output from the true gradient sums
+    std::vector<double> values(res.num_splits + 1);
+    GblCheck(gbl_learner_get_leaf_values(handle_, values.data(), res.num_splits + 1));
+    for (int leaf = 0; leaf <= res.num_splits; ++leaf) tree->SetLeafOutput(leaf, values[leaf]);
+  }
   if (res.num_splits == 0) Log::Warning("No further splits with positive gain");
   return tree.release();
 }

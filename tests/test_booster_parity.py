@@ -77,3 +77,20 @@ def test_predict_matches_reference_on_our_model(gpu):
     ours = ob.predict(X[:500].astype(np.float64), raw_score=True)
     ref_loaded = R.RefBooster.from_model_string(ob.model_to_string())
     np.testing.assert_allclose(ours, ref_loaded.predict(X[:500].astype(np.float64), raw_score=True), rtol=1e-12, atol=1e-12)
+
+
+def test_quant_train_renew_leaf(gpu):
+    """GradientDiscretizer::RenewIntGradTreeOutput (gradient_discretizer.cpp:209-260): same integer tree, leaf outputs
+    recomputed from the true gradient sums (fp64 sums in a different order -> tolerance)."""
+    X, y = H.make_binary(30000, 20, seed=23, nan_frac=0.05, zero_frac=0.2)
+    params = ("objective=binary num_leaves=31 learning_rate=0.1 min_data_in_leaf=20 use_quantized_grad=true "
+              "stochastic_rounding=false quant_train_renew_leaf=true lambda_l1=0.1 lambda_l2=1.0")
+    rb, ob = _train_both(X, y, params, 8)
+    _compare_models(rb, ob, rtol=1e-5)
+    np.testing.assert_allclose(ob.train_scores(raw=True), rb.train_scores_raw(), rtol=1e-5, atol=1e-8)
+    # and it is not a no-op: without renewal the leaf values of the second tree differ visibly (the first tree's
+    # gradients take two values that quantize exactly for balanced labels)
+    rb2, ob2 = _train_both(X, y, params.replace("quant_train_renew_leaf=true", "quant_train_renew_leaf=false"), 2)
+    a = R.parse_model_trees(ob.model_to_string())[1]["leaf_value"]
+    b = R.parse_model_trees(ob2.model_to_string())[1]["leaf_value"]
+    assert a.shape != b.shape or np.max(np.abs(a - b)) > 1e-4
