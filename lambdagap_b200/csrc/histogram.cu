@@ -271,10 +271,10 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_quant_kernel(LearnerDev 
   QuantAcc acc;
   acc.sh = sh;
   acc.st = reinterpret_cast<int2*>(sh + kPlane) + warp * 32;
-  acc.rp = opaque_ptr(d.rec + blockIdx.y * kTile + lane);
+  acc.rp = opaque_ptr(d.rec + blockIdx.y * d.tile_stride + lane);
   acc.rs = static_cast<unsigned>(d.rec_stride);
   acc.col = opaque_u32(static_cast<unsigned>(__cvta_generic_to_shared(sh + lane)));
-  acc.ghp = d.rec + d.gh_off;
+  acc.ghp = d.rec + blockIdx.y * d.tile_stride + d.gh_off;
   acc.dev = &d;
   acc.inv_g = d.ts->q_inv_grad_scale;
   acc.inv_h = d.ts->q_inv_hess_scale;
@@ -292,16 +292,16 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_float_kernel(LearnerDev 
   FloatAcc acc;
   acc.sh = sh;
   acc.st = reinterpret_cast<int4*>(sh + 4 * kPlane) + warp * 32;
-  acc.rp = opaque_ptr(d.rec + blockIdx.y * kTile + lane);
+  acc.rp = opaque_ptr(d.rec + blockIdx.y * d.tile_stride + lane);
   acc.rs = static_cast<unsigned>(d.rec_stride);
   acc.col = opaque_u32(static_cast<unsigned>(__cvta_generic_to_shared(sh + lane)));
-  acc.ghp = d.rec + d.gh_off;
+  acc.ghp = d.rec + blockIdx.y * d.tile_stride + d.gh_off;
   acc.grad = d.grad;
   acc.hess = d.hess;
   acc.g_scale = d.ts->g_scale;
   acc.h_scale = d.ts->h_scale;
   // the first pass of a tree also converts the gradients (to_fixed: exact power-of-two fixed point, |value| <= 2^30);
-  // with several tiles only tile 0 writes them (the other tiles' CTAs compute the same values)
+  // with several tiles every tile block of a record carries its own copy of the pair, written by that tile's CTAs
   acc.convert = explicit_count < 0 && d.ts->waves == 0;
   hist_drive(d, acc, out, explicit_indices, explicit_count, kFloatFlushCap, 2);
 }
@@ -317,7 +317,9 @@ void histogram_setup() {
 void launch_histogram(const LearnerDev& d, const int* explicit_indices, int explicit_count, long long* explicit_out,
                       cudaStream_t s) {
   const int tiles = d.p.num_tiles;
-  const int gx = std::max(1, (kNumSM + tiles - 1) / tiles);
+  // one CTA per SM at most, all tiles resident at once: a ceil here (e.g. 5 tiles x 30 = 150 CTAs on 148 SMs) leaves
+  // two CTAs for a second round that doubles the launch time
+  const int gx = std::max(1, kNumSM / tiles);
   if (d.p.quantized) {
     // 16-bit halves hold sums of at most flush_cap rows: |g| <= bins/2, h <= bins (gradient_discretizer.cpp:105-127)
     int flush_cap = (65535 / std::max(1, d.p.num_grad_quant_bins)) & ~255;

@@ -11,7 +11,8 @@ struct LearnerDev {
   uint8_t* rec;            // learner-owned row records: [row][32 bins per tile ...][gradient pair], see learner.cu
   int64_t col_stride;
   int rec_stride;          // bytes between row records
-  int gh_off;              // byte offset of the gradient pair inside a record
+  int tile_stride;         // bytes between the 32-feature tiles of a record (32, or 64 when each tile carries a pair)
+  int gh_off;              // byte offset of the gradient pair inside a tile block
   int num_data;  // local rows
   const FeatMeta* meta;
   // per-tree state
@@ -81,7 +82,8 @@ __device__ __forceinline__ short discretize_row(const LearnerDev& d, int i, doub
 
 // prep.cu
 void launch_iota(int* out, int n, cudaStream_t s);
-void launch_build_records(uint8_t* rec, int rec_stride, const uint8_t* row_bins, int row_stride, int n, cudaStream_t s);
+void launch_build_records(uint8_t* rec, int rec_stride, int tile_stride, const uint8_t* row_bins, int row_stride, int n,
+                          cudaStream_t s);
 void launch_tree_begin(const LearnerDev& d, const int* bag_indices, int bag_count, cudaStream_t s);
 void launch_maxabs(const LearnerDev& d, cudaStream_t s);
 void launch_scales_and_convert(const LearnerDev& d, cudaStream_t s);

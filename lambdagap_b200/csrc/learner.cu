@@ -183,41 +183,44 @@ static void free_tree_buffers(Learner* L) {
   L->records_pinned = nullptr;
 }
 
-// Row records.  The histogram kernel gathers, per row, the row's bins and its gradient pair.  DRAM serves 64-byte
-// bursts, so two separate gathers (a 32-byte bin sector here, an 8-byte pair there) cost two bursts per row --
-// measured 181 B of DRAM traffic per row against 40 B algorithmic.  A record keeps both together:
-//   [32 bytes of bins per tile ...][gradient pair]   (float mode: int2 fixed point; quantized: int8 [hess, grad])
-// with the pair tucked into the unused tail of the last tile's sector when it fits (quantized Higgs: one 32-byte
-// record per row), else in one extra sector (float Higgs: 64-byte records = one burst per row).  The records belong
-// to the learner, not the dataset: gradients are per learner, and several learners may share one dataset.
-static void record_layout(int num_features, int num_tiles, bool quant, int* gh_off, int* stride) {
+// Row records.  The histogram kernel gathers, per row and 32-feature tile, the tile's bins and the row's gradient
+// pair.  DRAM serves 64-byte bursts, so two separate gathers (a 32-byte bin sector here, an 8-byte pair there) cost
+// two bursts -- measured 181 B of DRAM traffic per row against 40 B algorithmic on the Higgs shape.  A record keeps
+// them together, one block per tile:
+//   [32 bytes of bins of tile 0][pair + padding] [32 bytes of bins of tile 1][pair + padding] ...   (64 B per tile)
+// (float mode: int2 fixed point; quantized: int8 [hess, grad]); every tile block has its own copy of the pair
+// because every tile is accumulated by its own CTAs.  With a single tile whose unused tail has room for the pair
+// (quantized Higgs: 28 bins + 2 bytes) the record is just the 32-byte sector.  The records belong to the learner,
+// not the dataset: gradients are per learner, and several learners may share one dataset.
+static void record_layout(int num_features, int num_tiles, bool quant, int* gh_off, int* tile_stride, int* stride) {
   const int gh_bytes = quant ? 2 : 8;
-  const int lanes_last = num_features - kTile * (num_tiles - 1);
-  const int inside = kTile * (num_tiles - 1) + static_cast<int>(round_up(lanes_last, gh_bytes));
-  if (inside + gh_bytes <= kTile * num_tiles) {
+  const int inside = static_cast<int>(round_up(num_features, gh_bytes));
+  if (num_tiles == 1 && inside + gh_bytes <= kTile) {
     *gh_off = inside;
-    *stride = kTile * num_tiles;
+    *tile_stride = kTile;
   } else {
-    *gh_off = kTile * num_tiles;
-    *stride = kTile * num_tiles + 32;
+    *gh_off = kTile;
+    *tile_stride = 2 * kTile;
   }
+  *stride = *tile_stride * num_tiles;
 }
 
 static void build_records(Learner* L) {
   const Dataset* ds = L->ds;
   const bool quant = L->cfg.use_quantized_grad != 0;
-  int gh_off = 0, stride = 0;
-  record_layout(ds->num_features, ds->num_tiles, quant, &gh_off, &stride);
+  int gh_off = 0, tile_stride = 0, stride = 0;
+  record_layout(ds->num_features, ds->num_tiles, quant, &gh_off, &tile_stride, &stride);
   if (L->rec != nullptr && L->rec_quant == quant) return;
   cudaFree(L->rec);
   L->rec = nullptr;
   GBL_CUDA(cudaMalloc(&L->rec, static_cast<size_t>(ds->num_data) * stride + 64));
   GBL_CUDA(cudaMemsetAsync(L->rec, 0, static_cast<size_t>(ds->num_data) * stride + 64, L->stream));
-  launch_build_records(L->rec, stride, ds->row_bins, ds->row_stride, static_cast<int>(ds->num_data), L->stream);
+  launch_build_records(L->rec, stride, tile_stride, ds->row_bins, ds->row_stride, static_cast<int>(ds->num_data), L->stream);
   GBL_CUDA(cudaStreamSynchronize(L->stream));
   L->rec_quant = quant;
   L->dev.rec = L->rec;
   L->dev.rec_stride = stride;
+  L->dev.tile_stride = tile_stride;
   L->dev.gh_off = gh_off;
 }
 

@@ -145,22 +145,24 @@ __global__ void scales_kernel(LearnerDev d) {
   }
 }
 
-// copies the dataset's row-major bin mirror into the learner's row records (16 bytes per thread)
-__global__ void __launch_bounds__(256) build_records_kernel(uint8_t* __restrict__ rec, int rec_stride,
+// copies the dataset's row-major bin mirror into the learner's row records: tile t of row r (32 bytes) goes to
+// rec + r * rec_stride + t * tile_stride (16 bytes per thread)
+__global__ void __launch_bounds__(256) build_records_kernel(uint8_t* __restrict__ rec, int rec_stride, int tile_stride,
                                                             const uint8_t* __restrict__ row_bins, int row_stride, int n) {
   const int per_row = row_stride / 16;
   const long long total = static_cast<long long>(n) * per_row;
   for (long long e = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; e < total;
        e += static_cast<long long>(gridDim.x) * blockDim.x) {
     const long long r = e / per_row;
-    const int c = static_cast<int>(e - r * per_row);
+    const int c = static_cast<int>(e - r * per_row);  // 16-byte chunk of the row: tile c / 2, half c & 1
     const uint4 v = *reinterpret_cast<const uint4*>(row_bins + r * row_stride + c * 16);
-    *reinterpret_cast<uint4*>(rec + r * rec_stride + c * 16) = v;
+    *reinterpret_cast<uint4*>(rec + r * rec_stride + (c >> 1) * tile_stride + (c & 1) * 16) = v;
   }
 }
 
-void launch_build_records(uint8_t* rec, int rec_stride, const uint8_t* row_bins, int row_stride, int n, cudaStream_t s) {
-  GBL_LAUNCH(build_records_kernel, kNumSM * 16, 256, 0, s, rec, rec_stride, row_bins, row_stride, n);
+void launch_build_records(uint8_t* rec, int rec_stride, int tile_stride, const uint8_t* row_bins, int row_stride, int n,
+                          cudaStream_t s) {
+  GBL_LAUNCH(build_records_kernel, kNumSM * 16, 256, 0, s, rec, rec_stride, tile_stride, row_bins, row_stride, n);
 }
 
 void launch_iota(int* out, int n, cudaStream_t s) {
