@@ -78,7 +78,15 @@ class ClockSampler:
     def __init__(self, device):
         self.device = device
         self.proc = None
-        self.lines = []
+        self.lines = []   # (arrival time, csv line)
+        self.t0 = None    # timed region (time.time()), set by mark()
+        self.t1 = None
+
+    def mark(self, begin):
+        if begin:
+            self.t0 = time.time()
+        else:
+            self.t1 = time.time()
 
     def start(self):
         q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
@@ -86,7 +94,7 @@ class ClockSampler:
              "clocks_event_reasons.sw_power_cap")
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.device), "--query-gpu=" + q,
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "20"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
@@ -95,7 +103,7 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.lines.append(line.strip())
+            self.lines.append((time.time(), line.strip()))
 
     def stop(self):
         if self.proc is None:
@@ -107,7 +115,14 @@ class ClockSampler:
             self.proc.kill()
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
+        # samples that arrived inside the timed region; a region shorter than one nvidia-smi query (tens of ms)
+        # can miss all of them, then the warm-up steps right before it (same load, same sampler) stand in
+        inside = [ln for (t, ln) in self.lines if self.t0 is not None and self.t1 is not None and self.t0 <= t <= self.t1 + 0.05]
+        window = "timed region"
+        if not inside:
+            inside = [ln for (_, ln) in self.lines]
+            window = "warm-up + timed region (timed region shorter than one sample)"
+        for ln in inside:
             parts = [p.strip() for p in ln.split(",")]
             if len(parts) < 7:
                 continue
@@ -120,7 +135,7 @@ class ClockSampler:
                 if val.lower().startswith("active"):
                     reasons.add(name)
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "samples": len(sm), "reasons": sorted(reasons)}
+                "samples": len(sm), "window": window, "reasons": sorted(reasons)}
 
 
 def measured_peaks():
@@ -267,11 +282,12 @@ def main():
         capi.synchronize(device)
 
     # ---- value: device-resident iterations, CUDA events on the learner's stream, max over ranks
+    clocks = ClockSampler(device)
+    clocks.start()
     for _ in range(args.warmup):
         bst.update()
     barrier()
-    clocks = ClockSampler(device)
-    clocks.start()
+    clocks.mark(True)
     launches0 = capi.kernel_launch_count()
     lrn.timer_record(0)
     for _ in range(args.steps):
@@ -279,6 +295,7 @@ def main():
     lrn.timer_record(1)
     ms = lrn.timer_elapsed_ms(0, 1)
     barrier()
+    clocks.mark(False)
     clk = clocks.stop()
     launches = capi.kernel_launch_count() - launches0
     if world > 1:

@@ -72,7 +72,9 @@ typedef struct gbl_learner_config {
 
 /* One performed split = the arguments of Tree::Split (src/io/tree.cpp:60-74) as SerialTreeLearner::SplitInner
  * passes them (src/treelearner/serial_tree_learner.cpp:798-810).  Record k splits `leaf`; the left child keeps
- * id `leaf`, the right child gets id k+1 (include/LightGBM/tree.h:543-583). */
+ * id `leaf`, the right child gets id k+1 (include/LightGBM/tree.h:543-583).  The records come in the order of the
+ * reference's leaf-wise loop (serial_tree_learner.cpp:210-245: always the leaf with the largest gain next), whatever
+ * order the device expanded the nodes in. */
 typedef struct gbl_split_record {
   int32_t leaf;
   int32_t feature;       /* inner feature index */
@@ -163,7 +165,10 @@ GBL_API int gbl_learner_set_quant_random(gbl_learner* learner, const double* gra
                                          const double* hess_random_host, int64_t n);
 GBL_API int gbl_learner_set_quant_random_start(gbl_learner* learner, int32_t random_values_use_start);
 /* TreeLearner::Train (tree_learner.h:61): grows one tree from device gradients/hessians (score_t = float).
- * `records_host` must hold num_leaves-1 records.  Synchronises the learner's stream before returning. */
+ * `records_host` must hold num_leaves-1 records.  Synchronises the learner's stream before returning.
+ * Environment (read when the learner is created): GBL_USE_GRAPH=0 drives the tree from the host instead of replaying
+ * one CUDA graph; GBL_SPEC_LIMIT=n caps speculative expansions (0 = the reference's own order, one split per round);
+ * GBL_HIST_POOL_MB bounds the histogram pool.  None of them changes a result. */
 GBL_API int gbl_learner_train(gbl_learner* learner, const float* gradients_dev, const float* hessians_dev,
                               gbl_tree_result* result_host, gbl_split_record* records_host);
 /* Same with host gradients (the path taken when boosting is not on the device, cf.
