@@ -559,9 +559,10 @@ static void train_async(Learner* L, const float* grad_dev, const float* hess_dev
 }
 
 // kernels a tree launched, derived from the device's own counters (the graph replays a data-dependent number of
-// waves): prologue (tree_begin, index init, maxabs, scales, histogram, root_init, scan) + 5 per wave + the replay
+// waves): prologue (tree_begin, index init, maxabs, scales, histogram, root_init, scan, select) + 6 per wave + the
+// replay
 static long long kernels_of_tree(const Learner* L, const TreeState& t) {
-  return 7 + 5LL * t.waves + 1 + ((L->cfg.use_quantized_grad && L->cfg.quant_train_renew_leaf) ? 3 : 0);
+  return 8 + 6LL * t.waves + 1 + ((L->cfg.use_quantized_grad && L->cfg.quant_train_renew_leaf) ? 3 : 0);
 }
 
 static void train_finish(Learner* L, gbl_tree_result* result, gbl_split_record* records) {
@@ -574,7 +575,8 @@ static void train_finish(Learner* L, gbl_tree_result* result, gbl_split_record* 
   if (ns < 0 || ns > L->cfg.num_leaves - 1) fatal("learner: corrupt tree state (num_splits=%d)", ns);
   if (t.error != 0)
     fatal("learner: internal error %d while growing the tree (%s)", t.error,
-          t.error == 1 ? "the replay needed a node that was never expanded" : "expansion capacity exhausted");
+          t.error == 1 ? "the replay needed a node that was never expanded"
+                       : t.error == 2 ? "expansion capacity exhausted" : "a scan job was not reduced");
   if (L->tree_in_graph) g_kernel_launches.fetch_add(kernels_of_tree(L, t), std::memory_order_relaxed);
   if (L->profiling) {
     for (size_t i = 0; i + 1 < L->ev_used; i += 2) {
