@@ -125,3 +125,41 @@ def test_schedule_edge_shapes(gpu, case):
             assert ns == 0
         if case == "chain":
             assert prof["waves"] >= 8
+
+
+def test_many_leaves_replay_in_global_scratch(gpu):
+    """num_leaves large enough that the replay's compact node arrays no longer fit shared memory
+    (finalize_kernel falls back to a global scratch) and the speculation budget is in the thousands."""
+    infos, cols, g, h = _data(21, 60000, 12, signal=2.0)
+    prof, ns = _compare(infos, cols, g, h, True, dict(num_leaves=1200, min_data_in_leaf=3, min_sum_hessian_in_leaf=1e-3))
+    assert ns > 600
+
+
+def test_bagging_subset(gpu):
+    """SetBaggingData (tree_learner.h:79): the tree is grown on the bagged rows only -- the same tree the sequential
+    restatement grows on the extracted subset -- and the score update touches only those rows."""
+    infos, cols, g, h = _data(31, 50000, 10, signal=1.5)
+    rng = np.random.default_rng(3)
+    bag = np.sort(rng.choice(50000, size=31000, replace=False)).astype(np.int32)
+    kw = dict(num_leaves=31, min_data_in_leaf=40)
+    sub_cols = [c[bag] for c in cols]
+    root, recs, leaf_of_row = O.train_tree(sub_cols, infos, g[bag], h[bag], O.make_config(use_quantized_grad=0, **kw))
+    dds = capi.Dataset.from_bins(infos, cols)
+    lrn = capi.Learner(dds, capi.learner_config(use_quantized_grad=0, stochastic_rounding=0, **kw))
+    lrn.set_bagging_data(bag)
+    for rep in range(2):
+        res, ours = lrn.train_host(g, h)
+        assert res["num_splits"] == len(recs)
+        for k, (a, b) in enumerate(zip(ours, recs)):
+            for key in KEYS:
+                assert a[key] == b[key], "split %d %s: %s vs %s" % (k, key, a[key], b[key])
+        assign = lrn.leaf_assignment()
+        np.testing.assert_array_equal(assign[bag], leaf_of_row)
+        out = np.ones(50000, dtype=bool)
+        out[bag] = False
+        assert np.all(assign[out] == -1)  # rows outside the bag belong to no leaf
+    lrn.set_bagging_data(None)  # back to all rows
+    res, ours = lrn.train_host(g, h)
+    assert np.all(lrn.leaf_assignment() >= 0)
+    lrn.free()
+    dds.free()
