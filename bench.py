@@ -81,6 +81,10 @@ class ClockSampler:
         self.lines = []   # (arrival time, csv line)
         self.t0 = None    # timed region (time.time()), set by mark()
         self.t1 = None
+        self.load_end = None  # end of the same load continued after the timed region
+
+    def samples_since_start(self):
+        return len([1 for (t, _) in self.lines if self.t0 is not None and t >= self.t0])
 
     def mark(self, begin):
         if begin:
@@ -120,8 +124,12 @@ class ClockSampler:
         inside = [ln for (t, ln) in self.lines if self.t0 is not None and self.t1 is not None and self.t0 <= t <= self.t1 + 0.05]
         window = "timed region"
         if not inside:
+            end = self.load_end if self.load_end is not None else float("inf")
+            inside = [ln for (t, ln) in self.lines if self.t0 is not None and self.t0 <= t <= end + 0.05]
+            window = "timed region + the same load continued (timed region shorter than one nvidia-smi sample)"
+        if not inside:
             inside = [ln for (_, ln) in self.lines]
-            window = "warm-up + timed region (timed region shorter than one sample)"
+            window = "warm-up + timed region + the same load continued"
         for ln in inside:
             parts = [p.strip() for p in ln.split(",")]
             if len(parts) < 7:
@@ -296,12 +304,20 @@ def main():
     ms = lrn.timer_elapsed_ms(0, 1)
     barrier()
     clocks.mark(False)
-    clk = clocks.stop()
     launches = capi.kernel_launch_count() - launches0
     if world > 1:
         t = torch.tensor([ms], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
+    # The timed region lasts tens of milliseconds, one nvidia-smi sample takes longer: keep the SAME load running
+    # (untimed extra iterations, the same number on every rank) for ~0.6 s so that the sampler sees it
+    extra = int(min(400, max(8, 600.0 / max(1e-3, ms / args.steps))))
+    for _ in range(extra):
+        bst.update()
+    capi.synchronize(device)
+    clocks.load_end = time.time()
+    clk = clocks.stop()
+    clk["extra_untimed_steps_for_sampling"] = extra
     value = args.steps / (ms / 1e3)
 
     # ---- roofline of the dominant kernel (histogram construction): a second pass over the same K steps with
