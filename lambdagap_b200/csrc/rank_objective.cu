@@ -61,6 +61,10 @@ struct RankState {
   int* class_queries[3] = {nullptr, nullptr, nullptr};  // query ids per size class
   int class_count[3] = {0, 0, 0};
   int class_pad[3] = {0, 0, 0};  // bitonic size (power of two) per class
+  // the three size classes run side by side (the few very long queries would otherwise hold the GPU alone)
+  cudaStream_t aux[2] = {nullptr, nullptr};
+  cudaEvent_t fork = nullptr;
+  cudaEvent_t join[2] = {nullptr, nullptr};
 };
 
 __device__ inline bool is_binary_target(int t) {
@@ -305,8 +309,11 @@ __global__ void lambdarank_kernel(RankParams p, const int* __restrict__ queries,
   const int t = p.target;
   const int k = p.truncation_level;
 
-  // ---- load + sort
-  for (int i = tid; i < n_pad; i += nt) {
+  // ---- load + sort.  The arrays are laid out for the class-wide n_pad; the sort network only spans this query's own
+  // power of two (a 130-document query of the 129..1024 class sorts 256 elements, not 1024)
+  int np = 2;
+  while (np < cnt) np <<= 1;
+  for (int i = tid; i < np; i += nt) {
     s_score[i] = i < cnt ? q_score[i] : -INFINITY;
     s_idx[i] = i;
   }
@@ -322,9 +329,9 @@ __global__ void lambdarank_kernel(RankParams p, const int* __restrict__ queries,
     __syncthreads();
   } else if (sorted) {
     // bitonic network on (score desc, index asc): a total order, hence == std::stable_sort by score desc (:289-291)
-    for (int size = 2; size <= n_pad; size <<= 1) {
+    for (int size = 2; size <= np; size <<= 1) {
       for (int stride = size >> 1; stride > 0; stride >>= 1) {
-        for (int x = tid; x < (n_pad >> 1); x += nt) {
+        for (int x = tid; x < (np >> 1); x += nt) {
           const int lo = (x / stride) * (stride << 1) + (x % stride);
           const int hi = lo + stride;
           const bool up = ((lo & size) == 0);  // ascending position = "comes first" order
@@ -568,14 +575,33 @@ void rank_objective_free(Objective* o) {
   cudaFree(rs->inv_bdcg);
   cudaFree(rs->query_boundaries);
   for (int c = 0; c < 3; ++c) cudaFree(rs->class_queries[c]);
+  for (int a = 0; a < 2; ++a) {
+    if (rs->aux[a]) cudaStreamDestroy(rs->aux[a]);
+    if (rs->join[a]) cudaEventDestroy(rs->join[a]);
+  }
+  if (rs->fork) cudaEventDestroy(rs->fork);
   delete rs;
   o->rank = nullptr;
 }
 
 void rank_objective_get_gradients(Objective* o, const double* score, float* grad, float* hess, cudaStream_t s) {
   RankState* rs = o->rank;
-  for (int c = 0; c < 3; ++c) {
+  if (rs->fork == nullptr) {
+    GBL_CUDA(cudaEventCreateWithFlags(&rs->fork, cudaEventDisableTiming));
+    for (int a = 0; a < 2; ++a) {
+      GBL_CUDA(cudaStreamCreateWithFlags(&rs->aux[a], cudaStreamNonBlocking));
+      GBL_CUDA(cudaEventCreateWithFlags(&rs->join[a], cudaEventDisableTiming));
+    }
+  }
+  GBL_CUDA(cudaEventRecord(rs->fork, s));
+  // longest queries first and on their own streams: class 2 -> aux[0], class 0 -> aux[1], class 1 -> s
+  const int order[3] = {2, 0, 1};
+  cudaStream_t where[3] = {rs->aux[0], rs->aux[1], s};
+  for (int k = 0; k < 3; ++k) {
+    const int c = order[k];
     if (rs->class_count[c] == 0) continue;
+    cudaStream_t cs = where[k];
+    if (cs != s) GBL_CUDA(cudaStreamWaitEvent(cs, rs->fork, 0));
     const int pad = rs->class_pad[c];
     const bool smem_label = pad <= 8192;
     size_t smem = static_cast<size_t>(pad) * (8 + 4 + (smem_label ? 4 : 0)) + 32 * 8;
@@ -584,11 +610,15 @@ void rank_objective_get_gradients(Objective* o, const double* score, float* grad
       smem += static_cast<size_t>(pad) * 8;
     }
     if (smem_label) {
-      GBL_LAUNCH(lambdarank_kernel<true>, rs->class_count[c], kClassThreads[c], smem, s, rs->p, rs->class_queries[c], pad,
+      GBL_LAUNCH(lambdarank_kernel<true>, rs->class_count[c], kClassThreads[c], smem, cs, rs->p, rs->class_queries[c], pad,
                  score, grad, hess);
     } else {
-      GBL_LAUNCH(lambdarank_kernel<false>, rs->class_count[c], kClassThreads[c], smem, s, rs->p, rs->class_queries[c], pad,
+      GBL_LAUNCH(lambdarank_kernel<false>, rs->class_count[c], kClassThreads[c], smem, cs, rs->p, rs->class_queries[c], pad,
                  score, grad, hess);
+    }
+    if (cs != s) {
+      GBL_CUDA(cudaEventRecord(rs->join[k], cs));
+      GBL_CUDA(cudaStreamWaitEvent(s, rs->join[k], 0));
     }
   }
 }

@@ -116,11 +116,12 @@ def assert_tree_matches(ours, ref, shrinkage=1.0, bias=0.0, rtol=1e-5, exact_cou
     np.testing.assert_allclose(ours.split_gain[:ni], ref["split_gain"], rtol=max(rtol, 1e-5), err_msg=what + " split_gain (model text prints 6 digits)")
 
 
-def make_ranking(num_queries, f, seed=0, min_len=2, max_len=60, zero_frac=0.3, max_label=4):
+def make_ranking(num_queries, f, seed=0, min_len=2, max_len=60, zero_frac=0.3, max_label=4, median_len=None):
     """MSLR-shaped synthetic ranking data: query sizes ~ clipped lognormal, labels 0..max_label correlated with a
     linear score, some zero-inflated columns."""
     rng = np.random.default_rng(seed)
-    sizes = np.clip(rng.lognormal(mean=np.log(max(3, max_len / 3)), sigma=0.7, size=num_queries).astype(np.int64), min_len, max_len)
+    med = max(3, max_len / 3) if median_len is None else median_len
+    sizes = np.clip(rng.lognormal(mean=np.log(med), sigma=0.7, size=num_queries).astype(np.int64), min_len, max_len)
     n = int(sizes.sum())
     X = rng.normal(size=(n, f)).astype(np.float32)
     for c in range(0, f, 3):
