@@ -3,8 +3,9 @@
 // Layout conventions:
 //   * bins are *mapper* bins (what BinIterator::Get returns in the reference), one byte per cell;
 //   * canonical storage is column-major  col_bins[F][col_stride]  (partition, streaming histogram);
-//   * a row-major mirror  row_bins[N][row_stride]  (row_stride = 32 * num_tiles) serves gathers: one 32-byte
-//     sector per (row, 32-feature tile);
+//   * a row-major mirror  row_bins[N][row_stride]  (row_stride = 32 * num_tiles): one 32-byte sector per
+//     (row, 32-feature tile); every learner copies it into its own row records, which also carry the row's
+//     gradient pair (learner.cu: record_layout) -- that is what the histogram kernel gathers;
 //   * histograms live in HBM as  hist[slot][tile][256 bins][32 lanes]  of exact integers:
 //       float mode     : {int64 grad_fix, int64 hess_fix} fixed-point (power-of-two scale per tree)
 //       quantized mode : int64 = (int32 grad_sum << 32) | uint32 hess_sum   (the reference's 32-bit packing,

@@ -1,12 +1,13 @@
 // learner.cu -- host side of the device tree learner + its C ABI.
 //
 // Mirrors SerialTreeLearner::Train (src/treelearner/serial_tree_learner.cpp:179-245) and, with a communicator,
-// DataParallelTreeLearner (src/treelearner/data_parallel_tree_learner.cpp:123-463).  The whole leaf-wise loop
-// (up to num_leaves-1 dependent rounds of histogram -> scan/arg-max -> partition) is enqueued on one stream with
-// fixed launch shapes; every kernel reads the leaf it works on from device memory, so the host never waits
-// inside a tree (the reference CUDA learner synchronises twice per split,
-// src/treelearner/cuda/cuda_single_gpu_tree_learner.cpp:246-325).  With GBL_USE_GRAPH=1 (default) the round
-// sequence is captured once into a CUDA graph and replayed per tree.
+// DataParallelTreeLearner (src/treelearner/data_parallel_tree_learner.cpp:123-463).  The leaf-wise loop is run in
+// WAVES: all leaves that may still be needed are split together (partition -> histograms of the smaller children ->
+// scan of all children -> selection of the next wave), and the reference's one-split-at-a-time order is replayed at
+// the end.  Every kernel finds its work in device memory; the whole tree is one CUDA graph with a
+// WHILE conditional node around the wave (GBL_USE_GRAPH=0, stage profiling and the data-parallel learner drive the
+// waves from the host, reading the small tree state back once per wave).  The reference CUDA learner synchronises with the host
+// twice per split (src/treelearner/cuda/cuda_single_gpu_tree_learner.cpp:246-325).
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
