@@ -81,6 +81,7 @@ struct Learner {
   size_t ev_used = 0;
   gbl_profile prof{};
   cudaEvent_t timer[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t state_ready = nullptr;  // host-driven loop: the tree state of the last selection has reached the host
   bool tree_in_graph = false;        // the pending tree runs as a graph replay (launches counted at train_finish)
 };
 
@@ -366,6 +367,7 @@ static void learner_free(Learner* L) {
   cudaFree(L->tap_hist);
   if (L->ts_pinned) cudaFreeHost(L->ts_pinned);
   for (cudaEvent_t e : L->ev) cudaEventDestroy(e);
+  if (L->state_ready != nullptr) cudaEventDestroy(L->state_ready);
   for (cudaEvent_t e : L->timer) {
     if (e != nullptr) cudaEventDestroy(e);
   }
@@ -409,11 +411,11 @@ static void enqueue_prologue(Learner* L, cudaStream_t s, cudaGraphConditionalHan
   }
 }
 
-// `first_slot` / `num_slots`: the wave's fresh histogram slots (known to the host only in the host-driven loop)
-static void enqueue_wave(Learner* L, cudaStream_t s, cudaGraphConditionalHandle cond, int use_cond, int first_slot,
-                         int num_slots) {
+// A wave in two halves.  Front: split the wave's nodes and build the smaller children's histograms -- everything
+// it needs is on the device.  Back: (data-parallel: all-reduce of the wave's fresh slots, whose range only the
+// host-driven loop knows: `first_slot` / `num_slots`), scan of all children, selection of the next wave.
+static void enqueue_wave_front(Learner* L, cudaStream_t s) {
   const LearnerDev& d = L->dev;
-  const bool multi = L->comm != nullptr && L->comm->num_ranks > 1;
   {
     StageTimer tm(L, s, kStagePart);
     launch_partition(d, s);
@@ -422,6 +424,12 @@ static void enqueue_wave(Learner* L, cudaStream_t s, cudaGraphConditionalHandle 
     StageTimer tm(L, s, kStageHist);
     launch_histogram(d, nullptr, -1, nullptr, s);
   }
+}
+
+static void enqueue_wave_back(Learner* L, cudaStream_t s, cudaGraphConditionalHandle cond, int use_cond, int first_slot,
+                              int num_slots) {
+  const LearnerDev& d = L->dev;
+  const bool multi = L->comm != nullptr && L->comm->num_ranks > 1;
   if (multi && num_slots > 0) {
     // the wave's histograms + (smaller, larger) row counts in one all-reduce; replaces Network::ReduceScatter of
     // data_parallel_tree_learner.cpp:285-297 and the count sync of :457-458
@@ -457,15 +465,22 @@ static void enqueue_epilogue(Learner* L, cudaStream_t s) {
 // Host-driven loop (profiling and the data-parallel learner): the host reads the tree state after every wave.
 static void run_tree_host_loop(Learner* L, cudaStream_t s) {
   L->ev_used = 0;
+  if (L->state_ready == nullptr) GBL_CUDA(cudaEventCreateWithFlags(&L->state_ready, cudaEventDisableTiming));
   enqueue_prologue(L, s, 0, 0);
+  GBL_CUDA(cudaMemcpyAsync(L->ts_pinned, L->ts, sizeof(TreeState), cudaMemcpyDeviceToHost, s));
+  GBL_CUDA(cudaEventRecord(L->state_ready, s));
   for (;;) {
-    GBL_CUDA(cudaMemcpyAsync(L->ts_pinned, L->ts, sizeof(TreeState), cudaMemcpyDeviceToHost, s));
-    GBL_CUDA(cudaStreamSynchronize(s));
-    const TreeState& t = *L->ts_pinned;
+    // the front half needs nothing from the host: enqueue it before waiting for the state of the previous
+    // selection, so the GPU keeps working while the host reads it (a finished tree turns these launches into no-ops)
+    enqueue_wave_front(L, s);
+    GBL_CUDA(cudaEventSynchronize(L->state_ready));
+    const TreeState t = *L->ts_pinned;
     if (t.done) break;
     if (t.num_cand <= 0 || t.num_cand > L->dev.max_cand || t.num_slots + t.num_cand > L->dev.max_slots)
       fatal("learner: corrupt wave state (num_cand=%d, num_slots=%d)", t.num_cand, t.num_slots);
-    enqueue_wave(L, s, 0, 0, t.num_slots, t.last_wave ? 0 : t.num_cand);
+    enqueue_wave_back(L, s, 0, 0, t.num_slots, t.last_wave ? 0 : t.num_cand);
+    GBL_CUDA(cudaMemcpyAsync(L->ts_pinned, L->ts, sizeof(TreeState), cudaMemcpyDeviceToHost, s));
+    GBL_CUDA(cudaEventRecord(L->state_ready, s));
   }
   enqueue_epilogue(L, s);
 }
@@ -499,7 +514,8 @@ static void build_graph(Learner* L) {
     GBL_CUDA(cudaGraphAddNode(&loop, graph, tail.data(), tail.size(), &cp));
     cudaGraph_t body = cp.conditional.phGraph_out[0];
     GBL_CUDA(cudaStreamBeginCaptureToGraph(s, body, nullptr, nullptr, 0, cudaStreamCaptureModeThreadLocal));
-    enqueue_wave(L, s, cond, 1, 0, 0);
+    enqueue_wave_front(L, s);
+    enqueue_wave_back(L, s, cond, 1, 0, 0);
     GBL_CUDA(cudaStreamEndCapture(s, &got));
     // epilogue
     GBL_CUDA(cudaStreamBeginCaptureToGraph(s, graph, &loop, nullptr, 1, cudaStreamCaptureModeThreadLocal));
