@@ -21,7 +21,8 @@ struct LearnerDev {
   unsigned long long* bkey;   // [max_nodes] bit pattern of Node::bval where positive, else 0 (compact copy for the selection)
   unsigned char* expanded;    // [max_nodes] 1 once the node has been split
   Expand* wave;            // [max_cand + 1] nodes expanded by the current wave
-  int* idx[2];             // ping-pong index buffers (DataPartition::indices_)
+  int* idx[3];             // [0], [1]: ping-pong index buffers (DataPartition::indices_); [2]: 0..N-1, never written
+                           // after the learner is created -- the root's segment when there is no bagging
   // gradients
   const float* grad;       // inputs of this tree
   const float* hess;
@@ -79,6 +80,9 @@ __device__ __forceinline__ short discretize_row(const LearnerDev& d, int i, doub
   }
   return static_cast<short>((static_cast<int>(qg) << 8) | (static_cast<int>(qh) & 0xff));
 }
+
+// index buffer that receives the children of a node whose segment lives in buffer `buf`
+__host__ __device__ inline int child_buf(int buf) { return buf == 2 ? 0 : (buf ^ 1); }
 
 // prep.cu
 void launch_iota(int* out, int n, cudaStream_t s);

@@ -39,7 +39,7 @@ struct Learner {
   int* seg_unit_begin = nullptr;
   double* renew_sums = nullptr;             // [2 * num_leaves] true gradient sums per leaf (quant_train_renew_leaf)
   unsigned char* replay_scratch = nullptr;  // only for trees too large for the replay's shared memory
-  int* idx[2] = {nullptr, nullptr};
+  int* idx[3] = {nullptr, nullptr, nullptr};
   uint8_t* rec = nullptr;  // row records (bins + gradient pair), rebuilt when the gradient format changes
   bool rec_quant = false;
   short* gh_q = nullptr;
@@ -326,6 +326,8 @@ static Learner* learner_create(const Dataset* ds, const gbl_learner_config* cfg,
   GBL_CUDA(cudaMemset(L->ts, 0, sizeof(TreeState)));
   GBL_CUDA(cudaMalloc(&L->idx[0], sizeof(int) * (n + 32)));
   GBL_CUDA(cudaMalloc(&L->idx[1], sizeof(int) * (n + 32)));
+  GBL_CUDA(cudaMalloc(&L->idx[2], sizeof(int) * (n + 32)));
+  launch_iota(L->idx[2], static_cast<int>(n), L->stream);
   GBL_CUDA(cudaMalloc(&L->gh_q, sizeof(short) * n));
   GBL_CUDA(cudaMallocHost(&L->ts_pinned, sizeof(TreeState)));
   LearnerDev& d = L->dev;
@@ -336,6 +338,7 @@ static Learner* learner_create(const Dataset* ds, const gbl_learner_config* cfg,
   d.ts = L->ts;
   d.idx[0] = L->idx[0];
   d.idx[1] = L->idx[1];
+  d.idx[2] = L->idx[2];
   d.gh_q = L->gh_q;
   d.feature_mask = nullptr;
   d.rand_g = nullptr;
@@ -356,6 +359,7 @@ static void learner_free(Learner* L) {
   cudaFree(L->ts);
   cudaFree(L->idx[0]);
   cudaFree(L->idx[1]);
+  cudaFree(L->idx[2]);
   cudaFree(L->rec);
   cudaFree(L->gh_q);
   cudaFree(L->feature_mask);
@@ -576,10 +580,10 @@ static void train_async(Learner* L, const float* grad_dev, const float* hess_dev
 }
 
 // kernels a tree launched, derived from the device's own counters (the graph replays a data-dependent number of
-// waves): prologue (tree_begin, index init, maxabs, scales, histogram, root_init, scan, select) + 6 per wave + the
-// replay
+// waves): prologue (tree_begin, [bagged index copy], maxabs, scales, histogram, root_init, scan, select) + 6 per
+// wave + the replay
 static long long kernels_of_tree(const Learner* L, const TreeState& t) {
-  return 8 + 6LL * t.waves + 1 + ((L->cfg.use_quantized_grad && L->cfg.quant_train_renew_leaf) ? 3 : 0);
+  return (L->bag_indices != nullptr ? 8 : 7) + 6LL * t.waves + 1 + ((L->cfg.use_quantized_grad && L->cfg.quant_train_renew_leaf) ? 3 : 0);
 }
 
 static void train_finish(Learner* L, gbl_tree_result* result, gbl_split_record* records) {

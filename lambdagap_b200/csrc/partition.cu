@@ -203,7 +203,7 @@ __global__ void __launch_bounds__(kPlanThreads) part_plan_kernel(LearnerDev d) {
     for (int k = 0; k < 2; ++k) {
       Node& X = *ch[k];
       X.depth = P.depth + 1;
-      X.buf = P.buf ^ 1;
+      X.buf = child_buf(P.buf);
       X.parent = w.node;
       X.left = -1;
       X.ref_leaf = -1;
@@ -278,7 +278,7 @@ __global__ void __launch_bounds__(kPartThreads) part_scatter_kernel(LearnerDev d
     const int nwords = (c_end - c_begin + 31) >> 5;
     const int lefts_before = d.unit_left[u] - d.unit_left[w.part_unit_begin];
     const int* __restrict__ src = d.idx[nd.buf] + nd.begin;
-    int* __restrict__ dst = d.idx[nd.buf ^ 1] + nd.begin;
+    int* __restrict__ dst = d.idx[child_buf(nd.buf)] + nd.begin;
     const unsigned* __restrict__ bits = d.unit_bits + static_cast<size_t>(u) * kUnitWords;
     if (tid < kUnitWords) {  // two warps: exclusive prefix of the words' popcounts
       const unsigned word = tid < nwords ? bits[tid] : 0u;

@@ -19,7 +19,7 @@ __global__ void __launch_bounds__(256) copy_int_kernel(int* __restrict__ out, co
 
 // One CTA: resets the tree state for a new tree (SerialTreeLearner::BeforeTrain,
 // src/treelearner/serial_tree_learner.cpp:288-338) and sets the root up as the first wave's histogram job.
-__global__ void __launch_bounds__(256) tree_begin_kernel(LearnerDev d, int root_count) {
+__global__ void __launch_bounds__(256) tree_begin_kernel(LearnerDev d, int root_count, int root_buf) {
   const int tid = threadIdx.x;
   for (int l = tid; l < d.p.num_leaves; l += blockDim.x) {
     d.leaf_values[l] = 0.0;
@@ -60,7 +60,7 @@ __global__ void __launch_bounds__(256) tree_begin_kernel(LearnerDev d, int root_
     R.count = root_count;
     R.global_count = root_count;
     R.depth = 0;
-    R.buf = 0;
+    R.buf = root_buf;
     R.slot = 0;
     R.parent = -1;
     R.left = -1;
@@ -171,11 +171,10 @@ void launch_iota(int* out, int n, cudaStream_t s) {
 
 void launch_tree_begin(const LearnerDev& d, const int* bag_indices, int bag_count, cudaStream_t s) {
   const int root_count = bag_indices != nullptr ? bag_count : d.num_data;
-  GBL_LAUNCH(tree_begin_kernel, 1, 256, 0, s, d, root_count);
+  // without bagging the root's segment is the learner's constant 0..N-1 buffer: nothing to initialise per tree
+  GBL_LAUNCH(tree_begin_kernel, 1, 256, 0, s, d, root_count, bag_indices != nullptr ? 0 : 2);
   if (bag_indices != nullptr) {
     GBL_LAUNCH(copy_int_kernel, (bag_count + 255) / 256, 256, 0, s, d.idx[0], bag_indices, bag_count);
-  } else {
-    launch_iota(d.idx[0], d.num_data, s);
   }
 }
 
