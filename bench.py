@@ -309,15 +309,6 @@ def main():
         t = torch.tensor([ms], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
-    # The timed region lasts tens of milliseconds, one nvidia-smi sample takes longer: keep the SAME load running
-    # (untimed extra iterations, the same number on every rank) for ~0.6 s so that the sampler sees it
-    extra = int(min(400, max(8, 600.0 / max(1e-3, ms / args.steps))))
-    for _ in range(extra):
-        bst.update()
-    capi.synchronize(device)
-    clocks.load_end = time.time()
-    clk = clocks.stop()
-    clk["extra_untimed_steps_for_sampling"] = extra
     value = args.steps / (ms / 1e3)
 
     # ---- roofline of the dominant kernel (histogram construction): a second pass over the same K steps with
@@ -329,6 +320,16 @@ def main():
         bst.update()
     prof = lrn.profile(reset=True)
     lrn.set_profiling(False)
+    # The timed region lasts tens of milliseconds, one nvidia-smi sample takes longer: the SAME load keeps running
+    # (the profiling pass above, then untimed extra iterations, the same number on every rank) for ~0.6 s in total so
+    # that the sampler sees it
+    extra = int(min(400, max(8, 600.0 / max(1e-3, ms / args.steps) - 2 * args.steps)))
+    for _ in range(extra):
+        bst.update()
+    capi.synchronize(device)
+    clocks.load_end = time.time()
+    clk = clocks.stop()
+    clk["extra_untimed_steps_for_sampling"] = extra
     F = cfg["features"]
     gh_bytes = 2 if args.quantized else 8
     hist_entry = 8 if args.quantized else 16

@@ -158,8 +158,11 @@ struct TreeState {
   int num_segments;   // row segments = leaves of the grown tree (>= leaves of the final tree)
   int seg_units;
   int error;          // internal consistency failure (reported by train_finish)
+  int rp_nl;          // replay of the reference's loop: current number of leaves ...
+  int rp_ns;          // ... and of splits replayed so far (state kept across waves, see split.cu)
   unsigned scan_done_counter;
   unsigned pad;
+  int pad2[2];
   // float mode fixed-point scales (powers of two): value_fix = value * g_scale ; value = fix * g_inv
   double g_scale, g_inv, h_scale, h_inv;
   // quantized mode (GradientDiscretizer): grad_scale/hess_scale and inverses

@@ -42,6 +42,7 @@ struct LearnerDev {
   double* leaf_values;     // [num_leaves] outputs of the last tree in the reference's leaf numbering
   int* leaf_node;          // [num_leaves] node of every final leaf
   int* split_node;         // [num_leaves] node split by the k-th split of the final tree
+  unsigned char* replay_scratch;  // compact node arrays of the replay when they do not fit shared memory, else null
   int* seg_node;           // [max_slots] nodes that hold rows (leaves of the grown tree)
   int* seg_unit_begin;     // [max_slots + 1] prefix of score-update work units
   // stochastic rounding

@@ -48,6 +48,8 @@ __global__ void __launch_bounds__(256) tree_begin_kernel(LearnerDev d, int root_
     t.num_segments = 1;
     t.seg_units = 0;
     t.error = 0;
+    t.rp_nl = 1;
+    t.rp_ns = 0;
     t.scan_done_counter = 0;
     t.max_abs_g = 0.f;
     t.max_abs_h = 0.f;
