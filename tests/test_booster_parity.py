@@ -94,3 +94,13 @@ def test_quant_train_renew_leaf(gpu):
     a = R.parse_model_trees(ob.model_to_string())[1]["leaf_value"]
     b = R.parse_model_trees(ob2.model_to_string())[1]["leaf_value"]
     assert a.shape != b.shape or np.max(np.abs(a - b)) > 1e-4
+
+
+def test_long_quantized_boosting(gpu):
+    """Many iterations: late trees have flat gains and long chains (the shape that stresses the wave schedule);
+    quantized mode must stay bit-identical in structure to the reference all the way."""
+    X, y = H.make_binary(40000, 12, seed=31, nan_frac=0.03, zero_frac=0.2)
+    params = ("objective=binary num_leaves=63 learning_rate=0.2 min_data_in_leaf=20 use_quantized_grad=true "
+              "stochastic_rounding=false")
+    rb, ob = _train_both(X, y, params, 120)
+    _compare_models(rb, ob, rtol=1e-5)
