@@ -17,7 +17,7 @@ import subprocess
 import sys
 
 tag = sys.argv[1] if len(sys.argv) > 1 else "r1"
-CMD_LIST = ("GBL_USE_GRAPH=0 ncu --metrics gpu__time_duration.sum --clock-control none -s 430 -c 300 python bench.py "
+CMD_LIST = ("GBL_USE_GRAPH=0 ncu --metrics gpu__time_duration.sum --clock-control none -s 330 -c 400 python bench.py "
             "--steps 2 --warmup 3 --no-cpu-baseline")
 CMD_TRAFFIC = ("GBL_USE_GRAPH=0 ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum "
                "--clock-control none -k regex:hist_float -s 54 -c 36 python bench.py --steps 2 --warmup 3 --no-cpu-baseline")
@@ -66,6 +66,8 @@ with open("profiles/%s_launch_summary.md" % tag, "w") as fh:
     for k, v in tree:
         if k.startswith("find_best"):
             cur["find"] = v
+        elif k.startswith("select"):
+            v = v + cur.get("find", 0.0)
             if wave == 0:
                 fh.write("| 0 (root; before it: %s) | - | - | - | %.1f | %.1f |\n" % (", ".join(pre), cur.get("hist", 0.0), v))
             else:
