@@ -2,7 +2,8 @@
 //
 // Layout conventions:
 //   * bins are *mapper* bins (what BinIterator::Get returns in the reference), one byte per cell;
-//   * canonical storage is column-major  col_bins[F][col_stride]  (partition, streaming histogram);
+//   * canonical storage is column-major, one column per feature at FeatMeta::col_off, 4-bit packed when the feature
+//     has at most 16 bins (the reference's DenseBin<uint8_t, true>, src/io/dense_bin.hpp:69-82) -- read by the partition;
 //   * a row-major mirror  row_bins[N][row_stride]  (row_stride = 32 * num_tiles): one 32-byte sector per
 //     (row, 32-feature tile); every learner copies it into its own row records, which also carry the row's
 //     gradient pair (learner.cu: record_layout) -- that is what the histogram kernel gathers;
@@ -82,7 +83,9 @@ struct FeatMeta {
   int most_freq_bin;
   int real_index;
   int offset;  // most_freq_bin == 0 (FeatureMetainfo::offset, feature_histogram.hpp:1429-1433)
+  int bits;    // 8, or 4 when num_bin <= 16: two rows per byte, even row in the low nibble (dense_bin.hpp:69-82)
   double penalty;
+  long long col_off;  // byte offset of this feature's column in Dataset::col_bins
 };
 
 // SplitInfo (src/treelearner/split_info.hpp:22-54) restricted to numerical splits
@@ -195,13 +198,21 @@ struct Dataset {
   int64_t num_data = 0;
   int num_features = 0;
   int num_tiles = 0;
-  int64_t col_stride = 0;  // bytes between feature columns
   int row_stride = 0;      // bytes between rows of the mirror
-  uint8_t* col_bins = nullptr;
+  uint8_t* col_bins = nullptr;  // packed column store (FeatMeta::col_off / bits)
+  int64_t col_bytes = 0;
+  uint8_t* stage = nullptr;     // build-time only: one byte per cell, column-major
+  int64_t stage_stride = 0;
   uint8_t* row_bins = nullptr;
   FeatMeta* meta_dev = nullptr;
   FeatMeta* meta_host = nullptr;
 };
+
+// bin of `row` in a column of the store
+__host__ __device__ inline int read_col_bin(const uint8_t* col, int bits, int row) {
+  if (bits == 4) return (col[row >> 1] >> ((row & 1) << 2)) & 0xf;
+  return col[row];
+}
 
 struct DeviceGuard {
   int prev = -1;

@@ -116,10 +116,11 @@ static Dataset* alloc_dataset(const gbl_feature_meta* metas, int num_features, i
   ds->num_data = num_data;
   ds->num_features = num_features;
   ds->num_tiles = (num_features + kTile - 1) / kTile;
-  ds->col_stride = round_up(num_data, 128) + 128;
   ds->row_stride = ds->num_tiles * kTile;
-  GBL_CUDA(cudaMalloc(&ds->col_bins, static_cast<size_t>(ds->col_stride) * num_features));
-  GBL_CUDA(cudaMemset(ds->col_bins, 0, static_cast<size_t>(ds->col_stride) * num_features));
+  // build-time staging: one byte per cell, uniform column stride (freed once the packed store exists)
+  ds->stage_stride = round_up(num_data, 128) + 128;
+  GBL_CUDA(cudaMalloc(&ds->stage, static_cast<size_t>(ds->stage_stride) * num_features));
+  GBL_CUDA(cudaMemset(ds->stage, 0, static_cast<size_t>(ds->stage_stride) * num_features));
   GBL_CUDA(cudaMalloc(&ds->row_bins, static_cast<size_t>(ds->row_stride) * (num_data + 8)));
   ds->meta_host = new FeatMeta[num_features];
   for (int f = 0; f < num_features; ++f) {
@@ -131,6 +132,10 @@ static Dataset* alloc_dataset(const gbl_feature_meta* metas, int num_features, i
     m.real_index = metas[f].real_index;
     m.offset = metas[f].most_freq_bin == 0 ? 1 : 0;
     m.penalty = metas[f].penalty;
+    // the reference packs two rows per byte when a feature has at most 16 bins (bin.cpp:615-625 -> DenseBin<.., true>)
+    m.bits = metas[f].num_bin <= 16 ? 4 : 8;
+    m.col_off = ds->col_bytes;
+    ds->col_bytes += round_up(m.bits == 4 ? (num_data + 1) / 2 : num_data, 128) + 128;
   }
   GBL_CUDA(cudaMalloc(&ds->meta_dev, sizeof(FeatMeta) * num_features));
   GBL_CUDA(cudaMemcpy(ds->meta_dev, ds->meta_host, sizeof(FeatMeta) * num_features, cudaMemcpyHostToDevice));
@@ -139,15 +144,48 @@ static Dataset* alloc_dataset(const gbl_feature_meta* metas, int num_features, i
 
 static void build_row_mirror(Dataset* ds) {
   dim3 grid(static_cast<unsigned>((ds->num_data + 127) / 128), ds->num_tiles);
-  GBL_LAUNCH(transpose_to_rows_kernel, grid, 256, 0, 0, ds->col_bins, ds->col_stride, ds->row_bins, ds->row_stride,
+  GBL_LAUNCH(transpose_to_rows_kernel, grid, 256, 0, 0, ds->stage, ds->stage_stride, ds->row_bins, ds->row_stride,
              ds->num_data, ds->num_features);
   GBL_CUDA(cudaDeviceSynchronize());
+}
+
+// staging (one byte per cell) -> the column store: 8-bit columns copied, 4-bit columns two rows per byte with the
+// even row in the low nibble (dense_bin.hpp:69-82)
+__global__ void __launch_bounds__(256) pack_columns_kernel(const uint8_t* __restrict__ stage, int64_t stage_stride,
+                                                           const FeatMeta* __restrict__ meta, int64_t n,
+                                                           uint8_t* __restrict__ store) {
+  const int f = blockIdx.y;
+  const FeatMeta m = meta[f];
+  const uint8_t* src = stage + f * stage_stride;
+  uint8_t* dst = store + m.col_off;
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  if (m.bits == 4) {
+    const int64_t bytes = (n + 1) / 2;
+    for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < bytes; i += stride) {
+      const unsigned lo = src[2 * i] & 0xf;
+      const unsigned hi = 2 * i + 1 < n ? (src[2 * i + 1] & 0xf) : 0u;
+      dst[i] = static_cast<uint8_t>(lo | (hi << 4));
+    }
+  } else {
+    for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) dst[i] = src[i];
+  }
+}
+
+static void build_column_store(Dataset* ds) {
+  GBL_CUDA(cudaMalloc(&ds->col_bins, static_cast<size_t>(ds->col_bytes)));
+  GBL_CUDA(cudaMemset(ds->col_bins, 0, static_cast<size_t>(ds->col_bytes)));
+  dim3 grid(kNumSM * 2, ds->num_features);
+  GBL_LAUNCH(pack_columns_kernel, grid, 256, 0, 0, ds->stage, ds->stage_stride, ds->meta_dev, ds->num_data, ds->col_bins);
+  GBL_CUDA(cudaDeviceSynchronize());
+  cudaFree(ds->stage);
+  ds->stage = nullptr;
 }
 
 static void free_dataset(Dataset* ds) {
   if (ds == nullptr) return;
   DeviceGuard guard(ds->device);
   cudaFree(ds->col_bins);
+  cudaFree(ds->stage);
   cudaFree(ds->row_bins);
   cudaFree(ds->meta_dev);
   delete[] ds->meta_host;
@@ -168,10 +206,11 @@ int gbl_dataset_create_from_bins(const gbl_feature_meta* metas, int32_t num_feat
   try {
     DeviceGuard guard(device_id);
     for (int f = 0; f < num_features; ++f) {
-      GBL_CUDA(cudaMemcpy(ds->col_bins + f * ds->col_stride, columns_host[f], static_cast<size_t>(num_data),
+      GBL_CUDA(cudaMemcpy(ds->stage + f * ds->stage_stride, columns_host[f], static_cast<size_t>(num_data),
                           cudaMemcpyHostToDevice));
     }
     build_row_mirror(ds);
+    build_column_store(ds);
   } catch (...) {
     free_dataset(ds);
     throw;
@@ -214,10 +253,11 @@ int gbl_dataset_create_from_mat_f32(const gbl_feature_meta* metas, int32_t num_f
                           cudaMemcpyHostToDevice));
       dim3 grid(static_cast<unsigned>((rows + 255) / 256), num_features);
       GBL_LAUNCH(value_to_bin_kernel, grid, 256, 0, 0, chunk_dev, r0, rows, num_total_columns, ds->meta_dev, off_dev,
-                 bounds_dev, num_features, ds->col_bins, ds->col_stride);
+                 bounds_dev, num_features, ds->stage, ds->stage_stride);
     }
     GBL_CUDA(cudaDeviceSynchronize());
     build_row_mirror(ds);
+    build_column_store(ds);
   } catch (...) {
     cudaFree(off_dev);
     cudaFree(bounds_dev);
@@ -251,8 +291,14 @@ int gbl_dataset_get_feature_bins(const gbl_dataset* ds_, int32_t feature, uint8_
   if (ds == nullptr || out_host == nullptr) fatal("gbl_dataset_get_feature_bins: null argument");
   if (feature < 0 || feature >= ds->num_features) fatal("gbl_dataset_get_feature_bins: feature out of range");
   DeviceGuard guard(ds->device);
-  GBL_CUDA(cudaMemcpy(out_host, ds->col_bins + feature * ds->col_stride, static_cast<size_t>(ds->num_data),
-                      cudaMemcpyDeviceToHost));
+  const FeatMeta& m = ds->meta_host[feature];
+  if (m.bits == 4) {  // unpack on the host
+    std::vector<uint8_t> packed(static_cast<size_t>((ds->num_data + 1) / 2));
+    GBL_CUDA(cudaMemcpy(packed.data(), ds->col_bins + m.col_off, packed.size(), cudaMemcpyDeviceToHost));
+    for (int64_t i = 0; i < ds->num_data; ++i) out_host[i] = static_cast<uint8_t>(read_col_bin(packed.data(), 4, static_cast<int>(i)));
+  } else {
+    GBL_CUDA(cudaMemcpy(out_host, ds->col_bins + m.col_off, static_cast<size_t>(ds->num_data), cudaMemcpyDeviceToHost));
+  }
   GBL_API_END();
 }
 

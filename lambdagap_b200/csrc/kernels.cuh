@@ -9,7 +9,6 @@ struct LearnerDev {
   // dataset
   const uint8_t* col_bins;
   uint8_t* rec;            // learner-owned row records: [row][32 bins per tile ...][gradient pair], see learner.cu
-  int64_t col_stride;
   int rec_stride;          // bytes between row records
   int tile_stride;         // bytes between the 32-feature tiles of a record (32, or 64 when each tile carries a pair)
   int gh_off;              // byte offset of the gradient pair inside a tile block

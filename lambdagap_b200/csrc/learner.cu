@@ -335,7 +335,6 @@ static Learner* learner_create(const Dataset* ds, const gbl_learner_config* cfg,
   GBL_CUDA(cudaMallocHost(&L->ts_pinned, sizeof(TreeState)));
   LearnerDev& d = L->dev;
   d.col_bins = ds->col_bins;
-  d.col_stride = ds->col_stride;
   d.num_data = static_cast<int>(ds->num_data);
   d.meta = ds->meta_dev;
   d.ts = L->ts;

@@ -31,6 +31,7 @@ constexpr int kPlanThreads = 1024;
 
 struct SplitRule {
   const uint8_t* col;
+  int bits;  // 8 or 4 (packed column)
   int threshold;
   int missing_bin;  // -1 = none
   bool default_left;
@@ -39,7 +40,8 @@ struct SplitRule {
 __device__ inline SplitRule load_rule(const LearnerDev& d, const BestSplit& bs) {
   const FeatMeta m = d.meta[bs.feature];
   SplitRule r;
-  r.col = d.col_bins + static_cast<int64_t>(bs.feature) * d.col_stride;
+  r.col = d.col_bins + m.col_off;
+  r.bits = m.bits;
   r.threshold = static_cast<int>(bs.threshold);
   r.missing_bin = -1;
   if (m.missing_type == GBL_MISSING_ZERO) r.missing_bin = m.default_bin;
@@ -49,7 +51,7 @@ __device__ inline SplitRule load_rule(const LearnerDev& d, const BestSplit& bs) 
 }
 
 __device__ inline bool goes_left(const SplitRule& r, int row) {
-  const int bin = __ldg(r.col + row);
+  const int bin = r.bits == 4 ? ((__ldg(r.col + (row >> 1)) >> ((row & 1) << 2)) & 0xf) : __ldg(r.col + row);
   return bin == r.missing_bin ? r.default_left : bin <= r.threshold;
 }
 
@@ -92,8 +94,14 @@ __global__ void __launch_bounds__(kPartThreads) part_count_kernel(LearnerDev d) 
       const int i = c_begin + k * kPartThreads + warp * 32 + lane;
       rows[k] = i < c_end ? src[i] : -1;
     }
+    if (rule.bits == 4) {  // CTA-uniform
 #pragma unroll
-    for (int k = 0; k < kIters; ++k) bins[k] = rows[k] >= 0 ? static_cast<int>(__ldg(rule.col + rows[k])) : -1;
+      for (int k = 0; k < kIters; ++k)
+        bins[k] = rows[k] >= 0 ? ((__ldg(rule.col + (rows[k] >> 1)) >> ((rows[k] & 1) << 2)) & 0xf) : -1;
+    } else {
+#pragma unroll
+      for (int k = 0; k < kIters; ++k) bins[k] = rows[k] >= 0 ? static_cast<int>(__ldg(rule.col + rows[k])) : -1;
+    }
     int cnt = 0;
 #pragma unroll
     for (int k = 0; k < kIters; ++k) {

@@ -62,6 +62,7 @@ static int* noalloc_scratch_for_current_device() {
 
 struct NoAllocRule {
   const uint8_t* col;
+  int bits;
   int threshold;
   int missing_bin;  // -1 = none
   int default_left;
@@ -69,7 +70,7 @@ struct NoAllocRule {
 
 // same decision as DenseBin::SplitInner in mapper-bin terms (see partition.cu)
 __device__ inline bool noalloc_goes_left(const NoAllocRule& r, int row) {
-  const int bin = r.col[row];
+  const int bin = read_col_bin(r.col, r.bits, row);
   return bin == r.missing_bin ? (r.default_left != 0) : bin <= r.threshold;
 }
 
@@ -185,7 +186,8 @@ int gbl_partition_rows_noalloc(const gbl_dataset* ds_, int32_t feature, uint32_t
   } else {
     const FeatMeta& m = ds->meta_host[feature];
     NoAllocRule rule;
-    rule.col = ds->col_bins + static_cast<int64_t>(feature) * ds->col_stride;
+    rule.col = ds->col_bins + m.col_off;
+    rule.bits = m.bits;
     rule.threshold = static_cast<int>(threshold_bin);
     rule.missing_bin = -1;
     if (m.missing_type == GBL_MISSING_ZERO) rule.missing_bin = m.default_bin;

@@ -171,3 +171,21 @@ def test_bagging_subset(gpu):
     assert np.all(lrn.leaf_assignment() >= 0)
     lrn.free()
     dds.free()
+
+
+def test_packed_columns_round_trip(gpu):
+    """Column store: features with at most 16 bins are kept 4-bit packed (two rows per byte, even row in the low
+    nibble, src/io/dense_bin.hpp:69-82); both views of the dataset must return the bins that went in, for an odd row
+    count as well, and splits on packed features must partition like the sequential restatement."""
+    infos, cols, g, h = _data(41, 30001, 9)
+    dds = capi.Dataset.from_bins(infos, cols)
+    for f in range(len(cols)):
+        np.testing.assert_array_equal(dds.feature_bins(f), cols[f], err_msg="column store, feature %d" % f)
+        np.testing.assert_array_equal(dds.feature_bins(f, rowmajor=True), cols[f], err_msg="row mirror, feature %d" % f)
+    dds.free()
+    # only low-cardinality features: every split reads a packed column
+    keep = [f for f in range(len(cols)) if infos[f]["num_bin"] <= 16]
+    sub_infos = [dict(infos[f], real_index=i) for i, f in enumerate(keep)]
+    sub_cols = [cols[f] for f in keep]
+    prof, ns = _compare(sub_infos, sub_cols, g, h, True, dict(num_leaves=31, min_data_in_leaf=20))
+    assert ns >= 5
