@@ -190,6 +190,11 @@ GBL_API int gbl_learner_add_prediction_to_score_dev(gbl_learner* learner, double
                                                     double* score_dev);
 /* test taps */
 /* leaf id of every (local) row after the last tree: DataPartition (src/treelearner/data_partition.hpp) */
+/* With bagging data set: the score update of the rows OUTSIDE the bag -- each walks the last tree on its bins
+ * (GBDT::UpdateScore -> ScoreUpdater::AddScore(tree, out-of-bag indices), src/boosting/gbdt.cpp:505-513,
+ * Tree::AddPredictionToScore src/io/tree.cpp:193-230).  Asynchronous on the learner's stream; no-op without bagging. */
+GBL_API int gbl_learner_add_prediction_out_of_bag_dev(gbl_learner* learner, double shrinkage, double bias,
+                                                      double* score_dev);
 /* leaf outputs of the last tree in the reference's leaf numbering, as the device holds them (before shrinkage); with
  * quant_train_renew_leaf these are the renewed outputs of GradientDiscretizer::RenewIntGradTreeOutput
  * (src/treelearner/gradient_discretizer.cpp:209-260), which the split records do not carry */

@@ -57,6 +57,8 @@ struct Learner {
   int rand_start = 0;
   int* bag_indices = nullptr;
   int bag_count = 0;
+  int* oob_indices = nullptr;  // rows outside the bag (complement of bag_indices)
+  int oob_count = 0;
   float* grad_stage = nullptr;  // train_host staging
   float* hess_stage = nullptr;
   long long* tap_hist = nullptr;
@@ -368,6 +370,7 @@ static void learner_free(Learner* L) {
   cudaFree(L->rand_g);
   cudaFree(L->rand_h);
   cudaFree(L->bag_indices);
+  cudaFree(L->oob_indices);
   cudaFree(L->grad_stage);
   cudaFree(L->hess_stage);
   cudaFree(L->tap_hist);
@@ -727,6 +730,7 @@ int gbl_learner_set_bagging_data(gbl_learner* learner, const int32_t* used_indic
   drop_graph(L);
   if (used_indices_host == nullptr || num_used <= 0 || num_used >= L->ds->num_data) {
     cudaFree(L->bag_indices);
+  cudaFree(L->oob_indices);
     L->bag_indices = nullptr;
     L->bag_count = 0;
   } else {
@@ -735,6 +739,22 @@ int gbl_learner_set_bagging_data(gbl_learner* learner, const int32_t* used_indic
     if (L->bag_indices == nullptr) GBL_CUDA(cudaMalloc(&L->bag_indices, sizeof(int) * L->ds->num_data));
     GBL_CUDA(cudaMemcpy(L->bag_indices, used_indices_host, sizeof(int) * num_used, cudaMemcpyHostToDevice));
     L->bag_count = num_used;
+    // the complement, for the score update of the rows the tree is not trained on
+    const int n = static_cast<int>(L->ds->num_data);
+    std::vector<char> in_bag(n, 0);
+    for (int i = 0; i < num_used; ++i) {
+      const int r = used_indices_host[i];
+      if (r < 0 || r >= n || in_bag[r]) fatal("gbl_learner_set_bagging_data: indices must be distinct rows of the dataset");
+      in_bag[r] = 1;
+    }
+    std::vector<int> oob;
+    oob.reserve(n - num_used);
+    for (int r = 0; r < n; ++r) {
+      if (!in_bag[r]) oob.push_back(r);
+    }
+    if (L->oob_indices == nullptr) GBL_CUDA(cudaMalloc(&L->oob_indices, sizeof(int) * n));
+    GBL_CUDA(cudaMemcpy(L->oob_indices, oob.data(), sizeof(int) * oob.size(), cudaMemcpyHostToDevice));
+    L->oob_count = static_cast<int>(oob.size());
   }
   GBL_API_END();
 }
@@ -836,6 +856,19 @@ int gbl_learner_add_prediction_to_score_dev(gbl_learner* learner, double shrinka
   if (!L->has_tree) fatal("gbl_learner_add_prediction_to_score_dev: no tree trained yet");
   DeviceGuard guard(L->ds->device);
   launch_add_score(L->dev, L->leaf_values, shrinkage, bias, score_dev, L->stream);
+  GBL_API_END();
+}
+
+int gbl_learner_add_prediction_out_of_bag_dev(gbl_learner* learner, double shrinkage, double bias, double* score_dev) {
+  GBL_API_BEGIN();
+  Learner* L = LEARNER(learner);
+  if (L == nullptr || score_dev == nullptr) fatal("gbl_learner_add_prediction_out_of_bag_dev: null argument");
+  if (!L->has_tree) fatal("gbl_learner_add_prediction_out_of_bag_dev: no tree trained yet");
+  DeviceGuard guard(L->ds->device);
+  if (L->bag_indices != nullptr && L->oob_count > 0) {
+    launch_add_score_rows(L->dev, L->ds->row_bins, L->ds->row_stride, L->oob_indices, L->oob_count, L->leaf_values, shrinkage,
+                          bias, score_dev, L->stream);
+  }
   GBL_API_END();
 }
 

@@ -389,6 +389,40 @@ __global__ void __launch_bounds__(256) leaf_assign_kernel(LearnerDev d, int* __r
   }
 }
 
+// score[row] += scale * value(leaf(row)) + bias for rows that were NOT part of the tree's training subset (bagging):
+// the row walks the final tree on its bins (Tree::AddPredictionToScore with used_data_indices, src/io/tree.cpp:193-230;
+// the decision of Tree::NumericalDecisionInner, include/LightGBM/tree.h:329-350, in mapper-bin terms).  The tree is
+// the device-resident one: nodes the replay marked in_tree are inner nodes, the first node that is not is the leaf.
+__global__ void __launch_bounds__(256) add_score_rows_kernel(LearnerDev d, const uint8_t* __restrict__ row_bins,
+                                                             int row_stride, const int* __restrict__ rows, int num_rows,
+                                                             const double* __restrict__ leaf_values, double scale,
+                                                             double bias, double* __restrict__ score) {
+  if (d.ts->num_splits == 0) return;  // a tree without splits changes no score
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < num_rows; i += gridDim.x * blockDim.x) {
+    const int row = rows[i];
+    const uint8_t* bins = row_bins + static_cast<size_t>(row) * row_stride;
+    int n = 0;
+    while (d.nodes[n].in_tree) {
+      const Node& nd = d.nodes[n];
+      const FeatMeta& m = d.meta[nd.best.feature];
+      const int bin = bins[nd.best.feature];
+      int missing_bin = -1;
+      if (m.missing_type == GBL_MISSING_ZERO) missing_bin = m.default_bin;
+      if (m.missing_type == GBL_MISSING_NAN) missing_bin = m.num_bin - 1;
+      const bool left = bin == missing_bin ? nd.best.default_left != 0 : bin <= static_cast<int>(nd.best.threshold);
+      n = nd.left + (left ? 0 : 1);
+    }
+    score[row] += scale * leaf_values[d.nodes[n].ref_leaf] + bias;
+  }
+}
+
+void launch_add_score_rows(const LearnerDev& d, const uint8_t* row_bins, int row_stride, const int* rows, int num_rows,
+                           const double* leaf_values_dev, double scale, double bias, double* score, cudaStream_t s) {
+  if (num_rows <= 0) return;
+  GBL_LAUNCH(add_score_rows_kernel, kPartGrid, 256, 0, s, d, row_bins, row_stride, rows, num_rows, leaf_values_dev, scale,
+             bias, score);
+}
+
 void launch_partition(const LearnerDev& d, cudaStream_t s) {
   GBL_LAUNCH(part_count_kernel, kPartGrid, kPartThreads, 0, s, d);
   GBL_LAUNCH(part_plan_kernel, 1, kPlanThreads, 0, s, d);

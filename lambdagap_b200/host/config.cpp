@@ -144,6 +144,7 @@ void Config::Set(const std::string& parameters) {
     };
     const int int_max = std::numeric_limits<int16_t>::max();
     data_random_seed = next_short(0, int_max);
+    bagging_seed = next_short(0, int_max);
   }
 #define GET_INT(name) if (const std::string* v = get(#name)) name = std::stoi(*v)
 #define GET_DBL(name) if (const std::string* v = get(#name)) name = std::stod(*v)
@@ -166,6 +167,10 @@ void Config::Set(const std::string& parameters) {
   GET_DBL(min_sum_hessian_in_leaf);
   GET_DBL(bagging_fraction);
   GET_INT(bagging_freq);
+  GET_INT(bagging_seed);
+  GET_DBL(pos_bagging_fraction);
+  GET_DBL(neg_bagging_fraction);
+  GET_BOOL(bagging_by_query);
   GET_DBL(feature_fraction);
   GET_DBL(feature_fraction_bynode);
   GET_BOOL(extra_trees);
@@ -232,7 +237,14 @@ void Config::Set(const std::string& parameters) {
   if (linear_tree) Log::Fatal("linear_tree is not supported by the B200 learner");
   if (extra_trees) Log::Fatal("extra_trees is not supported by the B200 learner");
   if (feature_fraction < 1.0 || feature_fraction_bynode < 1.0) Log::Fatal("feature_fraction < 1 is not supported by the B200 learner");
-  if (bagging_freq > 0 && bagging_fraction < 1.0) Log::Fatal("bagging is not supported by the B200 learner's boosting loop");
+  if (bagging_freq > 0 && bagging_fraction < 1.0) {
+    if (use_quantized_grad)
+      Log::Fatal("bagging with use_quantized_grad is not supported by the B200 learner (the reference's bagged quantized "
+                 "LeafSplits::Init indexes the gradients by position, leaf_splits.hpp:185)");
+    if (tree_learner != "serial") Log::Fatal("bagging with tree_learner=%s is not supported by the B200 learner", tree_learner.c_str());
+    if (bagging_by_query) Log::Fatal("bagging_by_query is not supported by the B200 learner");
+  }
+  if (pos_bagging_fraction < 1.0 || neg_bagging_fraction < 1.0) Log::Fatal("balanced bagging is not supported by the B200 learner");
   if (max_bin > 255) Log::Fatal("max_bin=%d: the B200 learner stores one byte per cell (max_bin <= 255)", max_bin);
   if (num_leaves < 2) Log::Fatal("num_leaves must be at least 2");
   for (const char* k : {"monotone_constraints", "interaction_constraints", "forcedsplits_filename", "categorical_feature",

@@ -48,6 +48,33 @@ void GBDT::Init(const Config* config, const Dataset* train_data, ObjectiveFuncti
   hess_dev_ = static_cast<float*>(p);
 }
 
+// BaggingSampleStrategy (src/boosting/bagging.hpp): every row draws NextFloat() from the generator of its block of
+// 1024 rows (seeded bagging_seed + block, state carried from iteration to iteration) and is in the bag when the draw
+// is below bagging_fraction; the in-bag rows are handed to the learner in ascending order.  Block-wise generators
+// make the result independent of the number of threads, so this sequential version draws the reference's bag.
+void GBDT::Bagging(int iter) {
+  const bool enabled = config_->bagging_freq > 0 && config_->bagging_fraction < 1.0;
+  if (!enabled) return;
+  constexpr int kBlock = 1024;  // bagging_rand_block_
+  if (bagging_rands_.empty()) {
+    // ResetSampleConfig (bagging.hpp:139-201)
+    bag_data_cnt_ = static_cast<data_size_t>(config_->bagging_fraction * num_data_);
+    bag_data_indices_.resize(num_data_);
+    for (int i = 0; i < (num_data_ + kBlock - 1) / kBlock; ++i) bagging_rands_.emplace_back(config_->bagging_seed + i);
+    need_re_bagging_ = true;
+  }
+  if (!((bag_data_cnt_ < num_data_ && iter % config_->bagging_freq == 0) || need_re_bagging_)) return;
+  need_re_bagging_ = false;
+  data_size_t cnt = 0;
+  for (data_size_t i = 0; i < num_data_; ++i) {
+    // bagging.hpp:233: `NextFloat() < config_->bagging_fraction` (float promoted to double)
+    if (static_cast<double>(bagging_rands_[i / kBlock].NextFloat()) < config_->bagging_fraction) bag_data_indices_[cnt++] = i;
+  }
+  bag_data_cnt_ = cnt;
+  Log::Debug("Re-bagging, using %d data to train", bag_data_cnt_);
+  tree_learner_->SetBaggingData(nullptr, bag_data_indices_.data(), bag_data_cnt_);
+}
+
 double GBDT::BoostFromAverage() {
   // gbdt.cpp:319-343 (single GPU: no Network::GlobalSyncUpByMean)
   if (models_.empty() && !has_init_score_ && objective_function_ != nullptr && config_->boost_from_average) {
@@ -79,6 +106,7 @@ bool GBDT::TrainOneIter(const score_t* gradients, const score_t* hessians) {
     GblCheck(gbl_memcpy_h2d(device_id_, grad_dev_, gradients, sizeof(float) * num_data_));
     GblCheck(gbl_memcpy_h2d(device_id_, hess_dev_, hessians, sizeof(float) * num_data_));
   }
+  Bagging(iter_);  // GBDT::TrainOneIter -> data_sample_strategy_->Bagging(iter_, ...), gbdt.cpp:383
   const bool is_first_tree = models_.empty();
   std::unique_ptr<Tree> new_tree;
   bool score_updated = false;
@@ -88,6 +116,7 @@ bool GBDT::TrainOneIter(const score_t* gradients, const score_t* hessians) {
     // such trees in the reference, gbdt.cpp:408-419).
     bl->TrainAsync(grad_dev_, hess_dev_);
     bl->AddPredictionToScoreAsync(shrinkage_rate_, score_dev_);
+    bl->AddPredictionOutOfBagAsync(shrinkage_rate_, score_dev_);
     new_tree.reset(bl->FinishTrain());
     score_updated = true;
   } else {

@@ -67,6 +67,10 @@ struct Config {
   double min_sum_hessian_in_leaf = 1e-3;
   double bagging_fraction = 1.0;
   int bagging_freq = 0;
+  int bagging_seed = 3;
+  double pos_bagging_fraction = 1.0;
+  double neg_bagging_fraction = 1.0;
+  bool bagging_by_query = false;
   double feature_fraction = 1.0;
   double feature_fraction_bynode = 1.0;
   bool extra_trees = false;
@@ -308,6 +312,8 @@ class B200TreeLearner : public TreeLearner {
   // still on the device, and only then wait for the split records
   void TrainAsync(const score_t* gradients, const score_t* hessians);
   void AddPredictionToScoreAsync(double shrinkage, double* out_score) const;
+  // rows outside the bag (GBDT::UpdateScore, src/boosting/gbdt.cpp:505-513); no-op without bagging
+  void AddPredictionOutOfBagAsync(double shrinkage, double* out_score) const;
   Tree* FinishTrain();
 
  private:
@@ -347,6 +353,12 @@ class GBDT {
 
  private:
   double BoostFromAverage();
+  // BaggingSampleStrategy::Bagging (src/boosting/bagging.hpp:31-139), row-level bagging
+  void Bagging(int iter);
+  std::vector<Random> bagging_rands_;     // one generator per block of 1024 rows (bagging.hpp:170-174)
+  std::vector<data_size_t> bag_data_indices_;
+  data_size_t bag_data_cnt_ = 0;
+  bool need_re_bagging_ = false;
   gbl_comm* comm_ = nullptr;
   const Config* config_ = nullptr;
   const Dataset* train_data_ = nullptr;

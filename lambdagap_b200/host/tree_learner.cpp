@@ -135,6 +135,10 @@ void B200TreeLearner::AddPredictionToScoreAsync(double shrinkage, double* out_sc
   GblCheck(gbl_learner_add_prediction_to_score_dev(handle_, shrinkage, 0.0, out_score));
 }
 
+void B200TreeLearner::AddPredictionOutOfBagAsync(double shrinkage, double* out_score) const {
+  GblCheck(gbl_learner_add_prediction_out_of_bag_dev(handle_, shrinkage, 0.0, out_score));
+}
+
 Tree* B200TreeLearner::FinishTrain() {
   gbl_tree_result res;
   GblCheck(gbl_learner_train_finish(handle_, &res, records_.data()));

@@ -104,3 +104,23 @@ def test_long_quantized_boosting(gpu):
               "stochastic_rounding=false")
     rb, ob = _train_both(X, y, params, 120)
     _compare_models(rb, ob, rtol=1e-5)
+
+
+def test_bagging_binary(gpu):
+    """Row bagging in the boosting loop (BaggingSampleStrategy, src/boosting/bagging.hpp): same bag every iteration
+    as the reference (block-wise generators), tree on the bag, out-of-bag rows scored by walking the tree."""
+    X, y = H.make_binary(30000, 15, seed=41, nan_frac=0.05, zero_frac=0.2)
+    params = "objective=binary num_leaves=31 learning_rate=0.1 min_data_in_leaf=20 bagging_fraction=0.7 bagging_freq=2 bagging_seed=11"
+    rb, ob = _train_both(X, y, params, 9)
+    _compare_models(rb, ob, rtol=1e-5)
+    np.testing.assert_allclose(ob.train_scores(raw=True), rb.train_scores_raw(), rtol=1e-5, atol=1e-8)
+
+
+def test_example_lambdarank_conf(gpu):
+    """The parameters of the reference's examples/lambdarank/train.conf (config #1 of BASELINE.json) on a synthetic
+    ranking set: lambdarank + bagging_fraction=0.9 / bagging_freq=1, min_sum_hessian_in_leaf=5."""
+    X, y, group = H.make_ranking(300, 40, seed=8, min_len=5, max_len=80)
+    params = ("objective=lambdarank num_leaves=31 learning_rate=0.1 feature_fraction=1.0 bagging_freq=1 bagging_fraction=0.9 "
+              "min_data_in_leaf=50 min_sum_hessian_in_leaf=5.0")
+    rb, ob = _train_both(X, y, params, 12, group=group)
+    _compare_models(rb, ob, rtol=1e-5)
