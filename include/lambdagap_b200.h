@@ -195,6 +195,11 @@ GBL_API int gbl_learner_add_prediction_to_score_dev(gbl_learner* learner, double
  * Tree::AddPredictionToScore src/io/tree.cpp:193-230).  Asynchronous on the learner's stream; no-op without bagging. */
 GBL_API int gbl_learner_add_prediction_out_of_bag_dev(gbl_learner* learner, double shrinkage, double bias,
                                                       double* score_dev);
+/* Scores of ANOTHER dataset binned with the training data's mappers (validation data): every row walks the last tree
+ * (ScoreUpdater::AddScore(tree) on a validation set, src/boosting/score_updater.hpp:79-86 -> Tree::AddPredictionToScore,
+ * src/io/tree.cpp:153-191).  Asynchronous on the learner's stream. */
+GBL_API int gbl_learner_add_prediction_to_dataset_dev(gbl_learner* learner, const gbl_dataset* other, double shrinkage,
+                                                      double bias, double* score_dev);
 /* leaf outputs of the last tree in the reference's leaf numbering, as the device holds them (before shrinkage); with
  * quant_train_renew_leaf these are the renewed outputs of GradientDiscretizer::RenewIntGradTreeOutput
  * (src/treelearner/gradient_discretizer.cpp:209-260), which the split records do not carry */

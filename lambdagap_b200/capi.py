@@ -76,7 +76,7 @@ EXPORTED_SYMBOLS = [
     "gbl_learner_set_bagging_data", "gbl_learner_set_quant_random", "gbl_learner_set_quant_random_start",
     "gbl_learner_train", "gbl_learner_train_host", "gbl_learner_train_async", "gbl_learner_train_finish",
     "gbl_learner_add_prediction_to_score", "gbl_learner_add_prediction_to_score_dev",
-    "gbl_learner_add_prediction_out_of_bag_dev", "gbl_learner_get_leaf_values", "gbl_learner_get_leaf_assignment", "gbl_learner_get_leaf_indices", "gbl_learner_get_histogram",
+    "gbl_learner_add_prediction_out_of_bag_dev", "gbl_learner_add_prediction_to_dataset_dev", "gbl_learner_get_leaf_values", "gbl_learner_get_leaf_assignment", "gbl_learner_get_leaf_indices", "gbl_learner_get_histogram",
     "gbl_learner_get_discretized", "gbl_learner_histogram_words", "gbl_learner_construct_histogram",
     "gbl_learner_stream", "gbl_learner_set_profiling", "gbl_learner_get_profile", "gbl_learner_timer_record",
     "gbl_learner_timer_elapsed_ms",

@@ -872,6 +872,23 @@ int gbl_learner_add_prediction_out_of_bag_dev(gbl_learner* learner, double shrin
   GBL_API_END();
 }
 
+int gbl_learner_add_prediction_to_dataset_dev(gbl_learner* learner, const gbl_dataset* other, double shrinkage, double bias,
+                                              double* score_dev) {
+  GBL_API_BEGIN();
+  Learner* L = LEARNER(learner);
+  const Dataset* o = reinterpret_cast<const Dataset*>(other);
+  if (L == nullptr || o == nullptr || score_dev == nullptr) fatal("gbl_learner_add_prediction_to_dataset_dev: null argument");
+  if (!L->has_tree) fatal("gbl_learner_add_prediction_to_dataset_dev: no tree trained yet");
+  if (o->device != L->ds->device) fatal("gbl_learner_add_prediction_to_dataset_dev: datasets on different devices");
+  if (o->num_features != L->ds->num_features)
+    fatal("gbl_learner_add_prediction_to_dataset_dev: %d features, the training data has %d (same bin mappers required)",
+          o->num_features, L->ds->num_features);
+  DeviceGuard guard(L->ds->device);
+  launch_add_score_rows(L->dev, o->row_bins, o->row_stride, nullptr, static_cast<int>(o->num_data), L->leaf_values, shrinkage,
+                        bias, score_dev, L->stream);
+  GBL_API_END();
+}
+
 int gbl_learner_get_leaf_values(gbl_learner* learner, double* out_host, int32_t num_leaves) {
   GBL_API_BEGIN();
   Learner* L = LEARNER(learner);

@@ -389,7 +389,8 @@ __global__ void __launch_bounds__(256) leaf_assign_kernel(LearnerDev d, int* __r
   }
 }
 
-// score[row] += scale * value(leaf(row)) + bias for rows that were NOT part of the tree's training subset (bagging):
+// score[row] += scale * value(leaf(row)) + bias for rows that were NOT part of the tree's training subset (bagging, or
+// the rows of a validation dataset binned with the same mappers; rows == nullptr: every row):
 // the row walks the final tree on its bins (Tree::AddPredictionToScore with used_data_indices, src/io/tree.cpp:193-230;
 // the decision of Tree::NumericalDecisionInner, include/LightGBM/tree.h:329-350, in mapper-bin terms).  The tree is
 // the device-resident one: nodes the replay marked in_tree are inner nodes, the first node that is not is the leaf.
@@ -399,7 +400,7 @@ __global__ void __launch_bounds__(256) add_score_rows_kernel(LearnerDev d, const
                                                              double bias, double* __restrict__ score) {
   if (d.ts->num_splits == 0) return;  // a tree without splits changes no score
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < num_rows; i += gridDim.x * blockDim.x) {
-    const int row = rows[i];
+    const int row = rows != nullptr ? rows[i] : i;
     const uint8_t* bins = row_bins + static_cast<size_t>(row) * row_stride;
     int n = 0;
     while (d.nodes[n].in_tree) {
