@@ -60,13 +60,15 @@ __device__ inline int hist_owner(const Expand* __restrict__ w, int n, int u) {
 }
 
 // ------------------------------------------------------------------------------------------ quantized mode
-// smem: int32 hist[256 bins][32 lanes] + per-warp staging of 32 rows {row, packed (grad << 16) + hess}.
-// Hot loop per row and warp: LDS.64 (row info, broadcast) + LDG.U8 (32 bins = one sector) + ATOMS.ADD.
+// smem: int32 hist[256 bins][32 lanes] + per-warp staging of 32 rows (row ids, packed (grad << 16) + hess words).
+// Per batch of 32 rows and warp: 8 LDS.128 (row ids, broadcast) + 32 LDG.U8 (32 bins = one sector each, all in
+// flight together) + 8 LDS.128 (gradient words) + 32 ATOMS.ADD.
 struct QuantAcc {
   static constexpr int kPlanes = 1;
   static constexpr int kStageBytes = 8;
   int* sh;
-  int2* st;
+  int* sr;  // per-warp staging: row ids of the batch
+  int* sv;  // per-warp staging: packed gradient words of the batch
   const uint8_t* rp;
   unsigned rs, col;
   uint8_t* ghp;  // record base + gradient offset
@@ -75,13 +77,20 @@ struct QuantAcc {
   bool convert;
 
   __device__ __forceinline__ void accumulate(const int* __restrict__ indices, int r0, int r1, int warp, int lane) const {
-    for (int base = r0 + warp * 32; base < r1; base += kHistWarps * 32) {
-      const int my = base + lane;
-      int2 t = make_int2(0, 0);  // padding rows add 0 to bin(row 0)
-      if (my < r1) {
-        const int r = indices != nullptr ? indices[my] : my;
+    int base = r0 + warp * 32;
+    if (base >= r1) return;
+    int r_next = base + lane < r1 ? (indices != nullptr ? indices[base + lane] : base + lane) : -1;
+    for (; base < r1; base += kHistWarps * 32) {
+      const int r = r_next;
+      {  // row ids of the warp's next batch: in flight while this batch is accumulated
+        const int nx = base + kHistWarps * 32 + lane;
+        r_next = nx < r1 ? (indices != nullptr ? indices[nx] : nx) : -1;
+      }
+      sr[lane] = max(r, 0);  // padding rows add 0 to bin(row 0)
+      __syncwarp();
+      int q = 0;  // int16: high byte grad (signed), low byte hess
+      if (r >= 0) {
         short* rec_gh = reinterpret_cast<short*>(ghp + static_cast<size_t>(static_cast<unsigned>(r)) * rs);
-        int q;  // int16: high byte grad (signed), low byte hess
         if (convert) {  // root pass: GradientDiscretizer::DiscretizeGradients for this row, kept for the later waves
           const short packed = discretize_row(*dev, r, inv_g, inv_h);
           *rec_gh = packed;
@@ -90,24 +99,28 @@ struct QuantAcc {
         } else {
           q = *rec_gh;
         }
-        t = make_int2(r, ((q >> 8) << 16) + (q & 0xff));   // packed (grad << 16) + hess
       }
-      st[lane] = t;
+      // all 32 bin sectors of the batch are requested before the first one is consumed (memory-level parallelism:
+      // 33 loads in flight per warp instead of 16 + a dependent gradient load in front of them)
+      int bins[32];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const int4 rr = reinterpret_cast<const int4*>(sr)[k];
+        bins[4 * k + 0] = __ldg(rp + static_cast<size_t>(static_cast<unsigned>(rr.x)) * rs);
+        bins[4 * k + 1] = __ldg(rp + static_cast<size_t>(static_cast<unsigned>(rr.y)) * rs);
+        bins[4 * k + 2] = __ldg(rp + static_cast<size_t>(static_cast<unsigned>(rr.z)) * rs);
+        bins[4 * k + 3] = __ldg(rp + static_cast<size_t>(static_cast<unsigned>(rr.w)) * rs);
+      }
+      sv[lane] = r >= 0 ? ((q >> 8) << 16) + (q & 0xff) : 0;  // packed (grad << 16) + hess
       __syncwarp();
 #pragma unroll
-      for (int j0 = 0; j0 < 32; j0 += 16) {
-        int bins[16];
-        int vals[16];
-#pragma unroll
-        for (int u = 0; u < 16; ++u) {
-          const int2 q = st[j0 + u];
-          vals[u] = q.y;
-          bins[u] = __ldg(rp + static_cast<size_t>(static_cast<unsigned>(q.x)) * rs);
-        }
-#pragma unroll
-        for (int u = 0; u < 16; ++u) red_shared_add(col + bins[u] * (kTile * 4), vals[u]);
+      for (int k = 0; k < 8; ++k) {
+        const int4 vv = reinterpret_cast<const int4*>(sv)[k];
+        red_shared_add(col + bins[4 * k + 0] * (kTile * 4), vv.x);
+        red_shared_add(col + bins[4 * k + 1] * (kTile * 4), vv.y);
+        red_shared_add(col + bins[4 * k + 2] * (kTile * 4), vv.z);
+        red_shared_add(col + bins[4 * k + 3] * (kTile * 4), vv.w);
       }
-      __syncwarp();
     }
   }
   // flush + re-zero: widen (g16 | h16) to the reference's (g32 | h32) packing
@@ -129,14 +142,15 @@ struct QuantAcc {
 // ------------------------------------------------------------------------------------------ float mode
 // smem: 4 planes of int32 [256][32]: g_lo, g_hi, h_lo, h_hi (16-bit limbs of the 2^k fixed-point value, so no
 // carries are needed: lo limbs sum < 2^16 * 65536 rows, hi limbs < 2^15 * 65536 rows) + per-warp staging.
-// Hot loop per row and warp: LDS.128 + LDG.U8 + 4 ATOMS.ADD.
+// Per batch of 32 rows and warp: 8 LDS.128 (row ids) + 32 LDG.U8 in flight together + 16 LDS.128 + 128 ATOMS.ADD.
 constexpr int kFloatFlushCap = 65536;
 
 struct FloatAcc {
   static constexpr int kPlanes = 4;
   static constexpr int kStageBytes = 16;
   int* sh;
-  int4* st;
+  int* sr;   // per-warp staging: row ids of the batch
+  int2* sv;  // per-warp staging: fixed-point (grad, hess) of the batch
   const uint8_t* rp;
   unsigned rs, col;
   uint8_t* ghp;  // record base + gradient offset
@@ -146,13 +160,20 @@ struct FloatAcc {
   bool convert;
 
   __device__ __forceinline__ void accumulate(const int* __restrict__ indices, int r0, int r1, int warp, int lane) const {
-    for (int base = r0 + warp * 32; base < r1; base += kHistWarps * 32) {
-      const int my = base + lane;
-      int4 t = make_int4(0, 0, 0, 0);
-      if (my < r1) {
-        const int r = indices != nullptr ? indices[my] : my;
+    int base = r0 + warp * 32;
+    if (base >= r1) return;
+    int r_next = base + lane < r1 ? (indices != nullptr ? indices[base + lane] : base + lane) : -1;
+    for (; base < r1; base += kHistWarps * 32) {
+      const int r = r_next;
+      {  // row ids of the warp's next batch: in flight while this batch is accumulated
+        const int nx = base + kHistWarps * 32 + lane;
+        r_next = nx < r1 ? (indices != nullptr ? indices[nx] : nx) : -1;
+      }
+      sr[lane] = max(r, 0);  // padding rows add 0 to bin(row 0)
+      __syncwarp();
+      int2 v = make_int2(0, 0);
+      if (r >= 0) {
         uint8_t* rec_gh = ghp + static_cast<size_t>(static_cast<unsigned>(r)) * rs;
-        int2 v;
         if (convert) {  // root pass: float gradients -> fixed point, kept in the row record for the later waves
           v.x = __double2int_rn(static_cast<double>(grad[r]) * g_scale);
           v.y = __double2int_rn(static_cast<double>(hess[r]) * h_scale);
@@ -160,32 +181,34 @@ struct FloatAcc {
         } else {
           v = *reinterpret_cast<const int2*>(rec_gh);
         }
-        t = make_int4(r, v.x, v.y, 0);
       }
-      st[lane] = t;
+      // all 32 bin sectors of the batch are requested before the first one is consumed (memory-level parallelism:
+      // 33 loads in flight per warp instead of 8 + a dependent gradient load in front of them)
+      int bins[32];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const int4 rr = reinterpret_cast<const int4*>(sr)[k];
+        bins[4 * k + 0] = __ldg(rp + static_cast<size_t>(static_cast<unsigned>(rr.x)) * rs);
+        bins[4 * k + 1] = __ldg(rp + static_cast<size_t>(static_cast<unsigned>(rr.y)) * rs);
+        bins[4 * k + 2] = __ldg(rp + static_cast<size_t>(static_cast<unsigned>(rr.z)) * rs);
+        bins[4 * k + 3] = __ldg(rp + static_cast<size_t>(static_cast<unsigned>(rr.w)) * rs);
+      }
+      sv[lane] = v;
       __syncwarp();
 #pragma unroll
-      for (int j0 = 0; j0 < 32; j0 += 8) {
-        int bins[8];
-        int gv[8];
-        int hv[8];
-#pragma unroll
-        for (int u = 0; u < 8; ++u) {
-          const int4 q = st[j0 + u];
-          gv[u] = q.y;
-          hv[u] = q.z;
-          bins[u] = __ldg(rp + static_cast<size_t>(static_cast<unsigned>(q.x)) * rs);
-        }
-#pragma unroll
-        for (int u = 0; u < 8; ++u) {
-          const unsigned a = col + bins[u] * (kTile * 4);
-          red_shared_add(a, gv[u] & 0xffff);
-          red_shared_add(a + kPlane * 4, gv[u] >> 16);
-          red_shared_add(a + 2 * kPlane * 4, hv[u] & 0xffff);
-          red_shared_add(a + 3 * kPlane * 4, hv[u] >> 16);
-        }
+      for (int k = 0; k < 16; ++k) {
+        const int4 vv = reinterpret_cast<const int4*>(sv)[k];  // two rows: {g, h, g, h}
+        const unsigned a = col + bins[2 * k] * (kTile * 4);
+        red_shared_add(a, vv.x & 0xffff);
+        red_shared_add(a + kPlane * 4, vv.x >> 16);
+        red_shared_add(a + 2 * kPlane * 4, vv.y & 0xffff);
+        red_shared_add(a + 3 * kPlane * 4, vv.y >> 16);
+        const unsigned b = col + bins[2 * k + 1] * (kTile * 4);
+        red_shared_add(b, vv.z & 0xffff);
+        red_shared_add(b + kPlane * 4, vv.z >> 16);
+        red_shared_add(b + 2 * kPlane * 4, vv.w & 0xffff);
+        red_shared_add(b + 3 * kPlane * 4, vv.w >> 16);
       }
-      __syncwarp();
     }
   }
   __device__ __forceinline__ void flush(long long* __restrict__ dst_words, int lanes_used) const {
@@ -270,7 +293,8 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_quant_kernel(LearnerDev 
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   QuantAcc acc;
   acc.sh = sh;
-  acc.st = reinterpret_cast<int2*>(sh + kPlane) + warp * 32;
+  acc.sr = sh + kPlane + warp * 64;
+  acc.sv = acc.sr + 32;
   acc.rp = opaque_ptr(d.rec + blockIdx.y * d.tile_stride + lane);
   acc.rs = static_cast<unsigned>(d.rec_stride);
   acc.col = opaque_u32(static_cast<unsigned>(__cvta_generic_to_shared(sh + lane)));
@@ -291,7 +315,8 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_float_kernel(LearnerDev 
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   FloatAcc acc;
   acc.sh = sh;
-  acc.st = reinterpret_cast<int4*>(sh + 4 * kPlane) + warp * 32;
+  acc.sr = sh + 4 * kPlane + warp * 128;
+  acc.sv = reinterpret_cast<int2*>(acc.sr + 32);
   acc.rp = opaque_ptr(d.rec + blockIdx.y * d.tile_stride + lane);
   acc.rs = static_cast<unsigned>(d.rec_stride);
   acc.col = opaque_u32(static_cast<unsigned>(__cvta_generic_to_shared(sh + lane)));

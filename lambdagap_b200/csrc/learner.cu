@@ -730,9 +730,11 @@ int gbl_learner_set_bagging_data(gbl_learner* learner, const int32_t* used_indic
   drop_graph(L);
   if (used_indices_host == nullptr || num_used <= 0 || num_used >= L->ds->num_data) {
     cudaFree(L->bag_indices);
-  cudaFree(L->oob_indices);
+    cudaFree(L->oob_indices);
     L->bag_indices = nullptr;
+    L->oob_indices = nullptr;
     L->bag_count = 0;
+    L->oob_count = 0;
   } else {
     if (L->comm != nullptr && L->comm->num_ranks > 1) fatal("learner: bagging with the data-parallel learner is not supported");
     if (L->cfg.use_quantized_grad) fatal("learner: bagging with use_quantized_grad is not supported");
