@@ -35,9 +35,19 @@ extern "C" {
 #define GBL_OBJ_BINARY 1
 #define GBL_OBJ_LAMBDARANK 2
 
+/* metric kinds, src/metric/metric.cpp:20-133 (Metric::CreateMetric) */
+#define GBL_METRIC_L2 0
+#define GBL_METRIC_RMSE 1
+#define GBL_METRIC_L1 2
+#define GBL_METRIC_BINARY_LOGLOSS 3
+#define GBL_METRIC_BINARY_ERROR 4
+#define GBL_METRIC_AUC 5
+#define GBL_METRIC_NDCG 6
+
 typedef struct gbl_dataset gbl_dataset;
 typedef struct gbl_learner gbl_learner;
 typedef struct gbl_objective gbl_objective;
+typedef struct gbl_metric gbl_metric;
 typedef struct gbl_comm gbl_comm;
 
 /* Per used ("inner") feature: what FeatureMetainfo (src/treelearner/feature_histogram.hpp:25-38) and
@@ -291,6 +301,31 @@ GBL_API int gbl_objective_get_gradients(gbl_objective* obj, const double* score_
 GBL_API int gbl_objective_boost_from_score(gbl_objective* obj, double* out_init_score);
 /* ObjectiveFunction::IsConstantHessian() */
 GBL_API int gbl_objective_is_constant_hessian(gbl_objective* obj, int32_t* out);
+
+/* ---------------------------------------------------------------- src/metric (evaluation on device-resident scores) */
+typedef struct gbl_metric_config {
+  int32_t kind;            /* GBL_METRIC_* */
+  int32_t num_eval_at;     /* ndcg */
+  const int32_t* eval_at;  /* ndcg: positions, ascending as Config sorts them (src/io/config.cpp:287-288); <= 4096 */
+  int32_t num_label_gain;  /* ndcg */
+  int32_t reserved;
+  const double* label_gain; /* ndcg: [num_label_gain], default 2^i - 1 (dcg_calculator.cpp:33-43) */
+  double sigmoid;          /* binary_logloss / binary_error: > 0 = scores are raw and converted with
+                              1 / (1 + exp(-sigmoid * score)) (BinaryLogloss::ConvertOutput, binary_objective.hpp:167-169),
+                              the case `objective != nullptr` of BinaryMetric::Eval; <= 0 = scores are probabilities */
+} gbl_metric_config;
+
+/* Metric::Init(metadata, num_data) (include/LightGBM/metric.h:32): label / weight / query_boundaries are host arrays
+ * copied to the device; weight and query_boundaries may be NULL (ndcg needs the boundaries, auc takes no weights). */
+GBL_API int gbl_metric_create(const gbl_metric_config* config, int64_t num_data, const float* label_host,
+                              const float* weight_host, const int32_t* query_boundaries_host, int32_t num_queries,
+                              int32_t device_id, gbl_metric** out);
+GBL_API int gbl_metric_free(gbl_metric* metric);
+/* number of values Eval returns: one per eval_at position for ndcg (NDCGMetric::GetName, rank_metric.hpp:34-36), else 1 */
+GBL_API int gbl_metric_num_outputs(const gbl_metric* metric, int32_t* out);
+/* Metric::Eval(score, objective) (include/LightGBM/metric.h:47) on a DEVICE score vector: kernels on `stream`
+ * (NULL = the default stream), then a wait for the few result bytes.  out_host[gbl_metric_num_outputs()]. */
+GBL_API int gbl_metric_eval(gbl_metric* metric, const double* score_dev, void* stream, double* out_host);
 
 /* ---------------------------------------------------------------- device memory helpers for host languages
  * that have no CUDA runtime binding (the adapter keeps scores/gradients device-resident like

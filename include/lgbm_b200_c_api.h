@@ -9,6 +9,7 @@
 #ifndef LGBM_B200_C_API_H_
 #define LGBM_B200_C_API_H_
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -57,6 +58,16 @@ LGBM_B200_EXPORT int LGBM_BoosterUpdateOneIter(BoosterHandle handle, int* is_fin
 LGBM_B200_EXPORT int LGBM_BoosterUpdateOneIterCustom(BoosterHandle handle, const float* grad, const float* hess,
                                                      int* is_finished);
 /* src/c_api.cpp:2112,2119 */
+/* include/LightGBM/c_api.h:729 -- the data must be binned with the training data's mappers (create it with
+ * `reference` = the training dataset) and must be added before the first iteration */
+LGBM_B200_EXPORT int LGBM_BoosterAddValidData(BoosterHandle handle, const DatasetHandle valid_data);
+/* include/LightGBM/c_api.h:846,861,918 -- metrics are evaluated on the device-resident scores; data_idx 0 = training
+ * data, i = the i-th validation set */
+LGBM_B200_EXPORT int LGBM_BoosterGetEvalCounts(BoosterHandle handle, int* out_len);
+LGBM_B200_EXPORT int LGBM_BoosterGetEvalNames(BoosterHandle handle, const int len, int* out_len, const size_t buffer_len,
+                                              size_t* out_buffer_len, char** out_strs);
+LGBM_B200_EXPORT int LGBM_BoosterGetEval(BoosterHandle handle, int data_idx, int* out_len, double* out_results);
+
 LGBM_B200_EXPORT int LGBM_BoosterGetCurrentIteration(BoosterHandle handle, int* out_iteration);
 LGBM_B200_EXPORT int LGBM_BoosterNumberOfTotalModel(BoosterHandle handle, int* out_models);
 /* src/c_api.cpp:2200,2209 */

@@ -66,6 +66,14 @@ class ObjectiveConfig(ctypes.Structure):
                 ("reserved2", ctypes.c_int32), ("label_gain", ctypes.POINTER(ctypes.c_double))]
 
 
+class MetricConfig(ctypes.Structure):
+    _fields_ = [("kind", ctypes.c_int32), ("num_eval_at", ctypes.c_int32), ("eval_at", ctypes.POINTER(ctypes.c_int32)),
+                ("num_label_gain", ctypes.c_int32), ("reserved", ctypes.c_int32),
+                ("label_gain", ctypes.POINTER(ctypes.c_double)), ("sigmoid", ctypes.c_double)]
+
+
+METRIC_KINDS = {"l2": 0, "rmse": 1, "l1": 2, "binary_logloss": 3, "binary_error": 4, "auc": 5, "ndcg": 6}
+
 # every symbol include/lambdagap_b200.h declares (tests check that the .so exports all of them)
 EXPORTED_SYMBOLS = [
     "gbl_last_error", "gbl_device_count", "gbl_kernel_launch_count",
@@ -82,6 +90,7 @@ EXPORTED_SYMBOLS = [
     "gbl_learner_timer_elapsed_ms",
     "gbl_objective_create", "gbl_objective_free", "gbl_objective_get_gradients", "gbl_objective_boost_from_score",
     "gbl_objective_is_constant_hessian",
+    "gbl_metric_create", "gbl_metric_free", "gbl_metric_num_outputs", "gbl_metric_eval",
     "gbl_device_malloc", "gbl_device_free", "gbl_memcpy_h2d", "gbl_memcpy_d2h", "gbl_device_fill_f64",
     "gbl_device_synchronize", "gbl_partition_rows_noalloc",
 ]
@@ -423,6 +432,45 @@ class Learner:
     def free(self):
         if self.handle:
             lib().gbl_learner_free(self.handle)
+            self.handle = None
+
+
+class Metric:
+    """gbl_metric_*: one evaluation metric over a device-resident score vector (src/metric/*.hpp)."""
+
+    def __init__(self, kind, label, weight=None, query_boundaries=None, eval_at=(1, 2, 3, 4, 5), label_gain=None,
+                 sigmoid=0.0, device=0):
+        label = np.ascontiguousarray(label, dtype=np.float32)
+        cfg = MetricConfig()
+        cfg.kind = METRIC_KINDS[kind]
+        self._eval_at = np.ascontiguousarray(eval_at, dtype=np.int32)
+        if label_gain is None:
+            label_gain = [float((1 << i) - 1) for i in range(31)]
+        self._gain = np.ascontiguousarray(label_gain, dtype=np.float64)
+        cfg.num_eval_at = len(self._eval_at)
+        cfg.eval_at = self._eval_at.ctypes.data_as(ctypes.POINTER(ctypes.c_int32))
+        cfg.num_label_gain = len(self._gain)
+        cfg.label_gain = self._gain.ctypes.data_as(ctypes.POINTER(ctypes.c_double))
+        cfg.sigmoid = sigmoid
+        w = None if weight is None else np.ascontiguousarray(weight, dtype=np.float32)
+        qb = None if query_boundaries is None else np.ascontiguousarray(query_boundaries, dtype=np.int32)
+        self.handle = ctypes.c_void_p()
+        check(lib().gbl_metric_create(ctypes.byref(cfg), ctypes.c_int64(len(label)), _ptr(label),
+                                      _ptr(w) if w is not None else None, _ptr(qb) if qb is not None else None,
+                                      ctypes.c_int32(0 if qb is None else len(qb) - 1), ctypes.c_int32(device),
+                                      ctypes.byref(self.handle)))
+        n = ctypes.c_int32(0)
+        check(lib().gbl_metric_num_outputs(self.handle, ctypes.byref(n)))
+        self.num_outputs = n.value
+
+    def eval(self, score_dev, stream=None):
+        out = np.zeros(self.num_outputs, dtype=np.float64)
+        check(lib().gbl_metric_eval(self.handle, _dev(score_dev), ctypes.c_void_p(stream), _ptr(out)))
+        return out
+
+    def free(self):
+        if self.handle:
+            check(lib().gbl_metric_free(self.handle))
             self.handle = None
 
 

@@ -21,6 +21,7 @@ LGBM_EXPORTED_SYMBOLS = [
     "LGBM_BoosterPredictForMat", "LGBM_BoosterSaveModelToString", "LGBM_NetworkGetNcclUniqueId",
     "LGBM_NetworkInitWithNccl", "LGBM_NetworkFree", "LGBM_BoosterGetTrainScoreRaw",
     "LGBM_DatasetCreateFromMatWithSample", "LGBM_BoosterGetLearnerHandle", "LGBM_B200_FindBin",
+    "LGBM_BoosterAddValidData", "LGBM_BoosterGetEvalCounts", "LGBM_BoosterGetEvalNames", "LGBM_BoosterGetEval",
 ]
 
 _lib = None
@@ -115,6 +116,40 @@ class Booster:
         _check(lib().LGBM_BoosterUpdateOneIterCustom(self.handle, grad.ctypes.data_as(ctypes.c_void_p),
                                                      hess.ctypes.data_as(ctypes.c_void_p), ctypes.byref(fin)))
         return fin.value
+
+    def add_valid(self, valid_set):
+        """LGBM_BoosterAddValidData; `valid_set` must have been created with reference=<the training set>."""
+        _check(lib().LGBM_BoosterAddValidData(self.handle, valid_set.handle))
+        self._valid = getattr(self, "_valid", []) + [valid_set]
+
+    def eval_names(self):
+        n = ctypes.c_int(0)
+        _check(lib().LGBM_BoosterGetEvalCounts(self.handle, ctypes.byref(n)))
+        bufs = [ctypes.create_string_buffer(255) for _ in range(n.value)]
+        ptrs = (ctypes.c_char_p * n.value)(*map(ctypes.addressof, bufs))
+        out_n = ctypes.c_int(0)
+        need = ctypes.c_size_t(0)
+        _check(lib().LGBM_BoosterGetEvalNames(self.handle, ctypes.c_int(n.value), ctypes.byref(out_n), ctypes.c_size_t(255),
+                                              ctypes.byref(need), ptrs))
+        return [b.value.decode() for b in bufs]
+
+    def eval(self, data_idx):
+        """LGBM_BoosterGetEval: metric values on the training data (0) or the data_idx-th validation set."""
+        n = ctypes.c_int(0)
+        _check(lib().LGBM_BoosterGetEvalCounts(self.handle, ctypes.byref(n)))
+        out = np.zeros(max(n.value, 1), dtype=np.float64)
+        got = ctypes.c_int(0)
+        _check(lib().LGBM_BoosterGetEval(self.handle, ctypes.c_int(data_idx), ctypes.byref(got),
+                                         out.ctypes.data_as(ctypes.c_void_p)))
+        return out[:got.value]
+
+    def valid_scores(self, data_idx, raw=False):
+        n = ctypes.c_int64(0)
+        _check(lib().LGBM_BoosterGetNumPredict(self.handle, ctypes.c_int(data_idx), ctypes.byref(n)))
+        out = np.zeros(n.value, dtype=np.float64)
+        _check(lib().LGBM_BoosterGetPredict(self.handle, ctypes.c_int(data_idx), ctypes.byref(n),
+                                            out.ctypes.data_as(ctypes.c_void_p)))
+        return out
 
     def learner(self):
         """The C-ABI learner behind this booster, wrapped for timers / profiling (capi.Learner methods)."""

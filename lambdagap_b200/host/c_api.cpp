@@ -1,5 +1,6 @@
 // c_api.cpp -- the reference's C API names for the hot-path subset (see include/lgbm_b200_c_api.h).
 // Reference: src/c_api.cpp (Booster class :169-195, :410-423; API_BEGIN/API_END :38-52).
+#include <algorithm>
 #include <cstring>
 #include <mutex>
 
@@ -31,6 +32,8 @@ struct Booster {
   Config config;
   std::unique_ptr<ObjectiveFunction> objective;
   std::unique_ptr<GBDT> boosting;
+  std::vector<std::unique_ptr<Metric>> train_metric;
+  std::vector<std::vector<std::unique_ptr<Metric>>> valid_metrics;
   std::mutex mutex;
   Booster(const Dataset* train_data, const char* parameters) {
     config.Set(parameters ? parameters : "");
@@ -43,6 +46,32 @@ struct Booster {
     objective.reset(ObjectiveFunction::CreateObjectiveFunction(config.objective, config));
     boosting.reset(new GBDT());
     boosting->Init(&config, train_data, objective.get(), g_num_machines > 1 ? g_comm : nullptr);
+    // Booster::CreateObjectiveAndMetrics (src/c_api.cpp:216-227): one metric object per configured metric
+    for (const std::string& type : config.metric_types) {
+      std::unique_ptr<Metric> m(Metric::CreateMetric(type, config));
+      if (m == nullptr) continue;
+      m->Init(train_data->metadata(), train_data->num_data(), train_data->device_id());
+      train_metric.push_back(std::move(m));
+    }
+    boosting->AddTrainingMetrics(Wrap(train_metric));
+  }
+  static std::vector<const Metric*> Wrap(const std::vector<std::unique_ptr<Metric>>& v) {  // Common::ConstPtrInVectorWrapper
+    std::vector<const Metric*> out;
+    for (const auto& m : v) out.push_back(m.get());
+    return out;
+  }
+  // Booster::AddValidData (src/c_api.cpp:394-408)
+  void AddValidData(const Dataset* valid_data) {
+    std::lock_guard<std::mutex> lock(mutex);
+    std::vector<std::unique_ptr<Metric>> metrics;
+    for (const std::string& type : config.metric_types) {
+      std::unique_ptr<Metric> m(Metric::CreateMetric(type, config));
+      if (m == nullptr) continue;
+      m->Init(valid_data->metadata(), valid_data->num_data(), valid_data->device_id());
+      metrics.push_back(std::move(m));
+    }
+    boosting->AddValidDataset(valid_data, Wrap(metrics));
+    valid_metrics.push_back(std::move(metrics));
   }
 };
 
@@ -124,6 +153,51 @@ int LGBM_BoosterUpdateOneIterCustom(BoosterHandle handle, const float* grad, con
   Booster* b = reinterpret_cast<Booster*>(handle);
   std::lock_guard<std::mutex> lock(b->mutex);
   *is_finished = b->boosting->TrainOneIter(grad, hess) ? 1 : 0;
+  API_END();
+}
+
+int LGBM_BoosterAddValidData(BoosterHandle handle, const DatasetHandle valid_data) {
+  API_BEGIN();
+  reinterpret_cast<Booster*>(handle)->AddValidData(reinterpret_cast<const Dataset*>(valid_data));
+  API_END();
+}
+
+int LGBM_BoosterGetEvalCounts(BoosterHandle handle, int* out_len) {
+  API_BEGIN();
+  Booster* b = reinterpret_cast<Booster*>(handle);
+  int ret = 0;  // Booster::GetEvalCounts (src/c_api.cpp:836-843)
+  for (const auto& m : b->train_metric) ret += static_cast<int>(m->GetName().size());
+  *out_len = ret;
+  API_END();
+}
+
+int LGBM_BoosterGetEvalNames(BoosterHandle handle, const int len, int* out_len, const size_t buffer_len,
+                             size_t* out_buffer_len, char** out_strs) {
+  API_BEGIN();
+  Booster* b = reinterpret_cast<Booster*>(handle);
+  *out_buffer_len = 0;  // Booster::GetEvalNames (src/c_api.cpp:845-860)
+  int idx = 0;
+  for (const auto& m : b->train_metric) {
+    for (const auto& name : m->GetName()) {
+      if (idx < len && buffer_len > 0) {
+        std::memcpy(out_strs[idx], name.c_str(), std::min(name.size() + 1, buffer_len));
+        out_strs[idx][buffer_len - 1] = '\0';
+      }
+      *out_buffer_len = std::max(name.size() + 1, *out_buffer_len);
+      ++idx;
+    }
+  }
+  *out_len = idx;
+  API_END();
+}
+
+int LGBM_BoosterGetEval(BoosterHandle handle, int data_idx, int* out_len, double* out_results) {
+  API_BEGIN();
+  Booster* b = reinterpret_cast<Booster*>(handle);
+  std::lock_guard<std::mutex> lock(b->mutex);
+  const std::vector<double> res = b->boosting->GetEvalAt(data_idx);  // LGBM_BoosterGetEval (src/c_api.cpp:2200-2212)
+  *out_len = static_cast<int>(res.size());
+  for (size_t i = 0; i < res.size(); ++i) out_results[i] = res[i];
   API_END();
 }
 

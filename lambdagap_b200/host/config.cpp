@@ -128,6 +128,19 @@ static std::string ParseObjectiveAlias(const std::string& type) {
   return type;
 }
 
+static std::string ParseMetricAlias(const std::string& type) {
+  // include/LightGBM/config.h:1316-1344 (the metrics this library evaluates, plus "custom")
+  if (type == "regression" || type == "regression_l2" || type == "l2" || type == "mean_squared_error" || type == "mse") return "l2";
+  if (type == "l2_root" || type == "root_mean_squared_error" || type == "rmse") return "rmse";
+  if (type == "regression_l1" || type == "l1" || type == "mean_absolute_error" || type == "mae") return "l1";
+  if (type == "binary_logloss" || type == "binary") return "binary_logloss";
+  if (type == "ndcg" || type == "lambdarank" || type == "rank_xendcg" || type == "xendcg" || type == "xe_ndcg" ||
+      type == "xe_ndcg_mart" || type == "xendcg_mart")
+    return "ndcg";
+  if (type == "none" || type == "null" || type == "custom" || type == "na") return "custom";
+  return type;
+}
+
 void Config::Set(const std::string& parameters) {
   auto params = Str2Map(parameters);
   auto get = [&params](const char* key) -> const std::string* {
@@ -225,6 +238,30 @@ void Config::Set(const std::string& parameters) {
     parse_list(*v, &tmp);
     eval_at.clear();
     for (double d : tmp) eval_at.push_back(static_cast<int>(d));
+  }
+  std::sort(eval_at.begin(), eval_at.end());  // src/io/config.cpp:287-288
+  if (const std::string* v = get("is_provide_training_metric")) is_provide_training_metric = ParseBool("is_provide_training_metric", *v);
+  // GetMetricType (src/io/config.cpp:152-163): the listed metrics (aliases resolved, duplicates dropped), or the
+  // objective's own metric when none is given
+  {
+    auto parse_metrics = [this](const std::string& value) {
+      metric_types.clear();
+      std::string cur;
+      for (char ch : value + ",") {
+        if (ch == ',') {
+          if (!cur.empty()) {
+            const std::string type = ParseMetricAlias(cur);
+            if (std::find(metric_types.begin(), metric_types.end(), type) == metric_types.end()) metric_types.push_back(type);
+          }
+          cur.clear();
+        } else if (ch != ' ') {
+          cur.push_back(ch);
+        }
+      }
+    };
+    const std::string* v = get("metric");
+    if (v != nullptr) parse_metrics(*v);
+    if (metric_types.empty() && (v == nullptr || v->empty())) parse_metrics(objective);
   }
   Log::level = verbosity;
 

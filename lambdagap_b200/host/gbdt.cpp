@@ -17,6 +17,53 @@ GBDT::~GBDT() {
   if (score_dev_) gbl_device_free(device_id_, score_dev_);
   if (grad_dev_) gbl_device_free(device_id_, grad_dev_);
   if (hess_dev_) gbl_device_free(device_id_, hess_dev_);
+  for (double* p : valid_score_dev_) gbl_device_free(device_id_, p);
+}
+
+void* GBDT::Stream() const {
+  B200TreeLearner* bl = dynamic_cast<B200TreeLearner*>(tree_learner_.get());
+  return bl != nullptr ? gbl_learner_stream(bl->handle()) : nullptr;
+}
+
+void GBDT::AddValidDataset(const Dataset* valid_data, const std::vector<const Metric*>& valid_metrics) {
+  if (valid_data == nullptr) Log::Fatal("GBDT::AddValidDataset: no data");
+  // Dataset::CheckAlign (gbdt.cpp:186-188): same used features and bin mappers as the training data
+  if (valid_data->num_features() != train_data_->num_features() ||
+      valid_data->num_total_features() != train_data_->num_total_features()) {
+    Log::Fatal("Cannot add validation data, since it has different bin mappers with training data");
+  }
+  for (int f = 0; f < train_data_->num_features(); ++f) {
+    const BinMapper* a = train_data_->FeatureBinMapper(f);
+    const BinMapper* b = valid_data->FeatureBinMapper(f);
+    if (train_data_->RealFeatureIndex(f) != valid_data->RealFeatureIndex(f) || a->num_bin() != b->num_bin() ||
+        a->missing_type() != b->missing_type() || a->bin_upper_bound().size() != b->bin_upper_bound().size() ||
+        std::memcmp(a->bin_upper_bound().data(), b->bin_upper_bound().data(),  // bitwise: the NaN bin's bound is NaN
+                    sizeof(double) * a->bin_upper_bound().size()) != 0) {
+      Log::Fatal("Cannot add validation data, since it has different bin mappers with training data");
+    }
+  }
+  if (valid_data->device_id() != device_id_) Log::Fatal("Cannot add validation data that lives on another device");
+  if (iter_ > 0 || !models_.empty()) {
+    // gbdt.cpp:198-203 replays the model on the new data; only the last tree is device-resident here
+    Log::Fatal("Validation data must be added before the first boosting iteration");
+  }
+  void* p = nullptr;
+  GblCheck(gbl_device_malloc(device_id_, sizeof(double) * valid_data->num_data(), &p));
+  GblCheck(gbl_device_fill_f64(device_id_, static_cast<double*>(p), 0.0, valid_data->num_data()));
+  valid_data_.push_back(valid_data);
+  valid_score_dev_.push_back(static_cast<double*>(p));
+  valid_metrics_.push_back(valid_metrics);
+}
+
+std::vector<double> GBDT::GetEvalAt(int data_idx) const {
+  if (data_idx < 0 || data_idx > static_cast<int>(valid_score_dev_.size())) Log::Fatal("Check failed: data_idx >= 0 && data_idx <= valid sets");
+  std::vector<double> ret;
+  const std::vector<const Metric*>& metrics = data_idx == 0 ? training_metrics_ : valid_metrics_[data_idx - 1];
+  const double* score = data_idx == 0 ? score_dev_ : valid_score_dev_[data_idx - 1];
+  for (const Metric* m : metrics) {
+    for (double v : m->Eval(score, objective_function_, Stream())) ret.push_back(v);  // GBDT::EvalOneMetric
+  }
+  return ret;
 }
 
 void GBDT::Init(const Config* config, const Dataset* train_data, ObjectiveFunction* objective, gbl_comm* comm) {
@@ -85,6 +132,10 @@ double GBDT::BoostFromAverage() {
     if (std::fabs(init_score) > kEpsilon) {
       // ScoreUpdater::AddScore(val): one fill since all scores are still zero
       GblCheck(gbl_device_fill_f64(device_id_, score_dev_, init_score, num_data_));
+      // gbdt.cpp:331-334: the validation scores start from the same value
+      for (size_t i = 0; i < valid_score_dev_.size(); ++i) {
+        GblCheck(gbl_device_fill_f64(device_id_, valid_score_dev_[i], init_score, valid_data_[i]->num_data()));
+      }
       Log::Info("Start training from score %lf", init_score);
       return init_score;
     }
@@ -117,6 +168,11 @@ bool GBDT::TrainOneIter(const score_t* gradients, const score_t* hessians) {
     bl->TrainAsync(grad_dev_, hess_dev_);
     bl->AddPredictionToScoreAsync(shrinkage_rate_, score_dev_);
     bl->AddPredictionOutOfBagAsync(shrinkage_rate_, score_dev_);
+    // GBDT::UpdateScore (gbdt.cpp:519-522): every validation row walks the new tree, still on the device
+    for (size_t i = 0; i < valid_score_dev_.size(); ++i) {
+      GblCheck(gbl_learner_add_prediction_to_dataset_dev(bl->handle(), valid_data_[i]->device_handle(), shrinkage_rate_, 0.0,
+                                                         valid_score_dev_[i]));
+    }
     new_tree.reset(bl->FinishTrain());
     score_updated = true;
   } else {
@@ -133,6 +189,9 @@ bool GBDT::TrainOneIter(const score_t* gradients, const score_t* hessians) {
       if (objective_function_ != nullptr && !config_->boost_from_average && !has_init_score_) {
         init_score = objective_function_->BoostFromScore(0);
         GblCheck(gbl_device_fill_f64(device_id_, score_dev_, init_score, num_data_));
+        for (size_t i = 0; i < valid_score_dev_.size(); ++i) {
+          GblCheck(gbl_device_fill_f64(device_id_, valid_score_dev_[i], init_score, valid_data_[i]->num_data()));
+        }
       }
       new_tree->AsConstantTree(init_score, num_data_);
     } else {
@@ -150,8 +209,8 @@ bool GBDT::TrainOneIter(const score_t* gradients, const score_t* hessians) {
 }
 
 int64_t GBDT::GetNumPredictAt(int data_idx) const {
-  if (data_idx != 0) Log::Fatal("Only the training data (data_idx=0) is attached to this booster");
-  return num_data_;
+  if (data_idx < 0 || data_idx > static_cast<int>(valid_data_.size())) Log::Fatal("Check failed: data_idx >= 0 && data_idx <= valid sets");
+  return data_idx == 0 ? num_data_ : valid_data_[data_idx - 1]->num_data();
 }
 
 void GBDT::GetTrainScore(double* out) const {
@@ -159,16 +218,21 @@ void GBDT::GetTrainScore(double* out) const {
 }
 
 void GBDT::GetPredictAt(int data_idx, double* out_result, int64_t* out_len) {
-  if (data_idx != 0) Log::Fatal("Only the training data (data_idx=0) is attached to this booster");
-  GetTrainScore(out_result);
+  const int64_t n = GetNumPredictAt(data_idx);
+  if (data_idx == 0) {
+    GetTrainScore(out_result);
+  } else {
+    GblCheck(gbl_device_synchronize(device_id_));
+    GblCheck(gbl_memcpy_d2h(device_id_, out_result, valid_score_dev_[data_idx - 1], sizeof(double) * n));
+  }
   if (objective_function_ != nullptr) {
-    for (int i = 0; i < num_data_; ++i) {
+    for (int64_t i = 0; i < n; ++i) {
       double v;
       objective_function_->ConvertOutput(out_result + i, &v);
       out_result[i] = v;
     }
   }
-  *out_len = num_data_;
+  *out_len = n;
 }
 
 std::string GBDT::SaveModelToString(int start_iteration, int num_iteration) const {

@@ -106,9 +106,11 @@ struct Config {
   bool lambdarank_norm = true;
   double lambdagap_weight = 1.0;
   std::vector<double> label_gain;
-  // metric (accepted, evaluated by the caller)
+  // metric
   std::string metric = "";
+  std::vector<std::string> metric_types;  // Config::metric after GetMetricType (src/io/config.cpp:152-163)
   std::vector<int> eval_at;
+  bool is_provide_training_metric = false;
 
   // Config::Str2Map + Config::Set (src/io/config.cpp, config_auto.cpp alias table)
   void Set(const std::string& parameters);
@@ -280,6 +282,33 @@ class ObjectiveFunction {
   gbl_objective* handle_ = nullptr;
 };
 
+// ---- Metric: evaluation on device-resident scores behind the reference's interface (include/LightGBM/metric.h)
+class Metric {
+ public:
+  // Metric::CreateMetric (src/metric/metric.cpp:20-133): l2, rmse, l1, binary_logloss, binary_error, auc, ndcg;
+  // nullptr for "custom" / unknown names like the reference
+  static Metric* CreateMetric(const std::string& type, const Config& config);
+  ~Metric();
+  // label / weights / query boundaries of `metadata` are copied to the device at the first Eval
+  void Init(const Metadata& metadata, data_size_t num_data, int device_id);
+  const std::vector<std::string>& GetName() const { return name_; }
+  double factor_to_bigger_better() const { return bigger_better_ ? 1.0 : -1.0; }
+  // score: DEVICE pointer; kernels run on `stream` (the learner's), then the few result bytes are awaited
+  std::vector<double> Eval(const double* score, const ObjectiveFunction* objective, void* stream) const;
+
+ private:
+  Metric() {}
+  std::string type_;
+  Config config_;
+  std::vector<std::string> name_;
+  bool bigger_better_ = false;
+  const Metadata* metadata_ = nullptr;
+  data_size_t num_data_ = 0;
+  int device_id_ = 0;
+  mutable gbl_metric* handle_ = nullptr;
+  mutable bool handle_with_objective_ = false;
+};
+
 // ---- TreeLearner
 class TreeLearner {
  public:
@@ -339,6 +368,12 @@ class GBDT {
   void Init(const Config* config, const Dataset* train_data, ObjectiveFunction* objective, gbl_comm* comm);
   // GBDT::TrainOneIter (src/boosting/gbdt.cpp:346-454); host gradients for objective=custom, nullptr otherwise.
   bool TrainOneIter(const score_t* gradients, const score_t* hessians);
+  // GBDT::AddValidDataset (src/boosting/gbdt.cpp:184-226); before the first iteration only (the device keeps the
+  // last tree, not the whole model).  The metrics stay owned by the caller (the Booster), as in the reference.
+  void AddValidDataset(const Dataset* valid_data, const std::vector<const Metric*>& valid_metrics);
+  void AddTrainingMetrics(const std::vector<const Metric*>& training_metrics) { training_metrics_ = training_metrics; }
+  // GBDT::GetEvalAt (src/boosting/gbdt.cpp:620-640): 0 = training data, i > 0 = the i-th validation set
+  std::vector<double> GetEvalAt(int data_idx) const;
   int64_t GetNumPredictAt(int data_idx) const;
   void GetPredictAt(int data_idx, double* out_result, int64_t* out_len);  // GBDT::GetPredictAt: converted outputs
   void GetTrainScore(double* out) const;                                  // raw scores (device -> host)
@@ -372,6 +407,11 @@ class GBDT {
   int device_id_ = 0;
   bool has_init_score_ = false;
   double* score_dev_ = nullptr;
+  std::vector<const Dataset*> valid_data_;
+  std::vector<double*> valid_score_dev_;  // ScoreUpdater of each validation set (score_updater.hpp:22-125), in HBM
+  std::vector<std::vector<const Metric*>> valid_metrics_;
+  std::vector<const Metric*> training_metrics_;
+  void* Stream() const;
   float* grad_dev_ = nullptr;
   float* hess_dev_ = nullptr;
 };

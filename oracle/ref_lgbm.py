@@ -55,7 +55,7 @@ def _params(d):
 class RefDataset:
     """LGBM_DatasetCreateFromMat (src/c_api.cpp:1303) + LGBM_DatasetSetField (:1760)."""
 
-    def __init__(self, X, label=None, group=None, weight=None, params=None):
+    def __init__(self, X, label=None, group=None, weight=None, params=None, reference=None):
         X = np.ascontiguousarray(X)
         assert X.dtype in (np.float32, np.float64)
         self.handle = ctypes.c_void_p()
@@ -63,7 +63,8 @@ class RefDataset:
         dt = C_API_DTYPE_FLOAT32 if X.dtype == np.float32 else C_API_DTYPE_FLOAT64
         _check(lib().LGBM_DatasetCreateFromMat(
             X.ctypes.data_as(ctypes.c_void_p), ctypes.c_int(dt), ctypes.c_int32(self.n), ctypes.c_int32(self.f),
-            ctypes.c_int(1), ctypes.c_char_p(_params(params or {})), None, ctypes.byref(self.handle)))
+            ctypes.c_int(1), ctypes.c_char_p(_params(params or {})), reference.handle if reference is not None else None,
+            ctypes.byref(self.handle)))
         if label is not None:
             self.set_field("label", np.asarray(label, dtype=np.float32))
         if weight is not None:
@@ -124,6 +125,40 @@ class RefBooster:
         _check(lib().LGBM_BoosterUpdateOneIterCustom(self.handle, grad.ctypes.data_as(ctypes.c_void_p),
                                                      hess.ctypes.data_as(ctypes.c_void_p), ctypes.byref(fin)))
         return fin.value
+
+    def add_valid(self, valid_set):
+        """LGBM_BoosterAddValidData (src/c_api.cpp:2040)."""
+        _check(lib().LGBM_BoosterAddValidData(self.handle, valid_set.handle))
+        self._valid = getattr(self, "_valid", []) + [valid_set]
+
+    def eval_names(self):
+        n = ctypes.c_int(0)
+        _check(lib().LGBM_BoosterGetEvalCounts(self.handle, ctypes.byref(n)))
+        bufs = [ctypes.create_string_buffer(255) for _ in range(n.value)]
+        ptrs = (ctypes.c_char_p * n.value)(*map(ctypes.addressof, bufs))
+        out_n = ctypes.c_int(0)
+        need = ctypes.c_size_t(0)
+        _check(lib().LGBM_BoosterGetEvalNames(self.handle, ctypes.c_int(n.value), ctypes.byref(out_n), ctypes.c_size_t(255),
+                                              ctypes.byref(need), ptrs))
+        return [b.value.decode() for b in bufs]
+
+    def eval(self, data_idx):
+        """LGBM_BoosterGetEval (src/c_api.cpp:2200): metric values on the training data (0) or a validation set."""
+        n = ctypes.c_int(0)
+        _check(lib().LGBM_BoosterGetEvalCounts(self.handle, ctypes.byref(n)))
+        out = np.zeros(max(n.value, 1), dtype=np.float64)
+        got = ctypes.c_int(0)
+        _check(lib().LGBM_BoosterGetEval(self.handle, ctypes.c_int(data_idx), ctypes.byref(got),
+                                         out.ctypes.data_as(ctypes.c_void_p)))
+        return out[:got.value]
+
+    def valid_scores(self, data_idx):
+        n = ctypes.c_int64(0)
+        _check(lib().LGBM_BoosterGetNumPredict(self.handle, ctypes.c_int(data_idx), ctypes.byref(n)))
+        out = np.zeros(n.value, dtype=np.float64)
+        _check(lib().LGBM_BoosterGetPredict(self.handle, ctypes.c_int(data_idx), ctypes.byref(n),
+                                            out.ctypes.data_as(ctypes.c_void_p)))
+        return out
 
     def train_scores(self):
         n = ctypes.c_int64(0)

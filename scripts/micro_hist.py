@@ -1,5 +1,6 @@
 """Micro-benchmark of the histogram kernel alone through gbl_learner_construct_histogram: back-to-back launches on
 row subsets of different sizes (sorted random subsets = sparse leaves), CUDA-event timed on the learner stream."""
+import os
 import sys
 import numpy as np
 sys.path.insert(0, ".")
@@ -19,12 +20,13 @@ words = lrn.histogram_words()
 out = capi.DeviceBuffer(8 * words)
 out.upload(np.zeros(words, dtype=np.int64))
 gh = 2 if quant else 8
-for m in (n, 2_000_000, 500_000, 100_000, 20_000, 4_000, 512):
+for m in (n, 5_000_000, 2_000_000, 500_000, 100_000, 20_000, 4_000, 512):
     if m == n:
         idx = None
     else:
         idx = capi.DeviceBuffer.from_numpy(np.sort(rng.choice(n, size=m, replace=False)).astype(np.int32))
     reps = 20 if m > 1_000_000 else 200
+    reps = int(os.environ.get("MICRO_REPS", reps))  # 1 under ncu
     for _ in range(3):
         lrn.construct_histogram(idx, m, out)
     lrn.timer_record(0)

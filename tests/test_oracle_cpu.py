@@ -147,3 +147,52 @@ def test_config_rejects_what_the_learner_does_not_implement():
                 "monotone_constraints=1,0", "tree_learner=voting"):
         with pytest.raises(engine.LightGBMError):
             engine.Dataset(np.zeros((10, 2), dtype=np.float32), np.zeros(10, dtype=np.float32), params=bad + " verbose=-1")
+
+
+def test_metric_restatement_matches_reference():
+    """oracle/oracle_metrics.py against the unmodified reference: the reference evaluates its metrics on its own scores
+    (LGBM_BoosterGetEval), the restatement on the same scores (LGBM_BoosterGetPredict).  AUC is exact (integer
+    arithmetic in doubles); the means differ only in summation order."""
+    from oracle import oracle_metrics as M
+    from oracle import ref_lgbm as R
+    if not R.available():
+        pytest.skip("oracle/_ref not built")
+    rng = np.random.default_rng(0)
+    n, f, nv = 6000, 8, 2500
+    X = rng.normal(size=(n, f)).astype(np.float32)
+    y = (X[:, 0] + 0.5 * X[:, 1] * X[:, 2] + 0.5 * rng.normal(size=n) > 0).astype(np.float32)
+    Xv = rng.normal(size=(nv, f)).astype(np.float32)
+    yv = (Xv[:, 0] + 0.5 * Xv[:, 1] * Xv[:, 2] + 0.5 * rng.normal(size=nv) > 0).astype(np.float32)
+    ds = R.RefDataset(X, y, params="max_bin=63 verbose=-1")
+    dv = R.RefDataset(Xv, yv, params="max_bin=63 verbose=-1", reference=ds)
+    common = " num_leaves=7 verbose=-1 num_threads=2 min_data_in_leaf=200"
+    b = R.RefBooster(ds, "objective=binary metric=binary_logloss,auc,binary_error" + common)
+    b.add_valid(dv)
+    for _ in range(4):
+        b.update()
+    assert b.eval_names() == ["binary_logloss", "auc", "binary_error"]
+    for idx, lab in ((0, y), (1, yv)):
+        e = b.eval(idx)
+        p = b.train_scores() if idx == 0 else b.valid_scores(1)  # few distinct values: large tie groups
+        np.testing.assert_allclose(e[0], M.binary_logloss(p, lab), rtol=1e-13)
+        assert e[1] == M.auc(p, lab)
+        assert e[2] == M.binary_error(p, lab)
+    b = R.RefBooster(ds, "objective=regression metric=l2,rmse,l1,auc" + common)
+    b.add_valid(dv)
+    for _ in range(4):
+        b.update()
+    e, p = b.eval(1), b.valid_scores(1)
+    np.testing.assert_allclose(e[:3], [M.l2(p, yv), M.rmse(p, yv), M.l1(p, yv)], rtol=1e-13)
+    assert e[3] == M.auc(p, yv)
+    q = rng.integers(1, 60, size=150)
+    q[3] = 400
+    qb = np.concatenate(([0], np.cumsum(q)))
+    Xr = rng.normal(size=(qb[-1], f)).astype(np.float32)
+    yr = np.clip((Xr[:, 0] * 1.2 + rng.normal(size=qb[-1])).round(), 0, 4).astype(np.float32)
+    yr[qb[5]:qb[6]] = 0  # a query without relevant documents counts NDCG = 1
+    dr = R.RefDataset(Xr, yr, group=q.astype(np.int32), params="max_bin=63 verbose=-1")
+    b = R.RefBooster(dr, "objective=lambdarank metric=ndcg eval_at=1,3,5,10,500 num_leaves=7 verbose=-1 num_threads=2")
+    for _ in range(3):
+        b.update()
+    assert b.eval_names() == ["ndcg@1", "ndcg@3", "ndcg@5", "ndcg@10", "ndcg@500"]
+    np.testing.assert_allclose(b.eval(0), M.ndcg(b.train_scores(), yr, qb, [1, 3, 5, 10, 500]), rtol=1e-14)
