@@ -43,6 +43,7 @@ struct Learner {
   uint8_t* rec = nullptr;  // row records (bins + gradient pair), rebuilt when the gradient format changes
   bool rec_quant = false;
   short* gh_q = nullptr;
+  unsigned short* leaf_u16 = nullptr;  // leaf id per row, scratch of the score update
   long long* hist_pool = nullptr;
   size_t hist_pool_words = 0;
   unsigned char* splittable = nullptr;
@@ -334,6 +335,7 @@ static Learner* learner_create(const Dataset* ds, const gbl_learner_config* cfg,
   GBL_CUDA(cudaMalloc(&L->idx[2], sizeof(int) * (n + 32)));
   launch_iota(L->idx[2], static_cast<int>(n), L->stream);
   GBL_CUDA(cudaMalloc(&L->gh_q, sizeof(short) * n));
+  GBL_CUDA(cudaMalloc(&L->leaf_u16, sizeof(unsigned short) * (n + 8)));
   GBL_CUDA(cudaMallocHost(&L->ts_pinned, sizeof(TreeState)));
   LearnerDev& d = L->dev;
   d.col_bins = ds->col_bins;
@@ -366,6 +368,7 @@ static void learner_free(Learner* L) {
   cudaFree(L->idx[2]);
   cudaFree(L->rec);
   cudaFree(L->gh_q);
+  cudaFree(L->leaf_u16);
   cudaFree(L->feature_mask);
   cudaFree(L->rand_g);
   cudaFree(L->rand_h);
@@ -846,7 +849,7 @@ int gbl_learner_add_prediction_to_score(gbl_learner* learner, const double* leaf
   if (num_leaves < 1 || num_leaves > L->cfg.num_leaves) fatal("gbl_learner_add_prediction_to_score: bad num_leaves");
   DeviceGuard guard(L->ds->device);
   GBL_CUDA(cudaMemcpyAsync(L->leaf_values_tmp, leaf_values_host, sizeof(double) * num_leaves, cudaMemcpyHostToDevice, L->stream));
-  launch_add_score(L->dev, L->leaf_values_tmp, 1.0, 0.0, score_dev, L->stream);
+  launch_add_score(L->dev, L->leaf_values_tmp, 1.0, 0.0, score_dev, L->leaf_u16, L->bag_indices != nullptr, L->stream);
   GBL_CUDA(cudaStreamSynchronize(L->stream));
   GBL_API_END();
 }
@@ -857,7 +860,7 @@ int gbl_learner_add_prediction_to_score_dev(gbl_learner* learner, double shrinka
   if (L == nullptr || score_dev == nullptr) fatal("gbl_learner_add_prediction_to_score_dev: null argument");
   if (!L->has_tree) fatal("gbl_learner_add_prediction_to_score_dev: no tree trained yet");
   DeviceGuard guard(L->ds->device);
-  launch_add_score(L->dev, L->leaf_values, shrinkage, bias, score_dev, L->stream);
+  launch_add_score(L->dev, L->leaf_values, shrinkage, bias, score_dev, L->leaf_u16, L->bag_indices != nullptr, L->stream);
   GBL_API_END();
 }
 

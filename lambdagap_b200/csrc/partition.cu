@@ -376,6 +376,51 @@ __global__ void __launch_bounds__(256) add_score_kernel(LearnerDev d, const doub
   }
 }
 
+// Two-step score update for trees of at most 65535 leaves.  The scattered read-modify-write of 8-byte scores above
+// moves a 32-byte sector per row in both directions; writing a 2-byte leaf id per row instead is a plain store into an
+// array that stays in L2 (2 bytes x num_data), and the scores are then updated by one streaming pass.
+__global__ void __launch_bounds__(256) leaf_mark_kernel(LearnerDev d, unsigned short* __restrict__ out) {
+  const TreeState& t = *d.ts;
+  const int U = t.seg_units, S = t.num_segments;
+  for (int u = blockIdx.x; u < U; u += gridDim.x) {
+    const int si = seg_owner(d.seg_unit_begin, S, u);
+    const Node& nd = d.nodes[d.seg_node[si]];
+    const unsigned short leaf = static_cast<unsigned short>(nd.ref_leaf);
+    const int c_begin = (u - d.seg_unit_begin[si]) * kSegUnit;
+    const int c_end = min(nd.count, c_begin + kSegUnit);
+    const int* __restrict__ src = d.idx[nd.buf] + nd.begin;
+    for (int i = c_begin + threadIdx.x; i < c_end; i += 256) out[src[i]] = leaf;
+  }
+}
+
+// score[row] += scale * leaf_value[leaf(row)] + bias, four rows per thread; 0xFFFF = row outside the tree's rows (bagging)
+__global__ void __launch_bounds__(256) add_score_dense_kernel(const unsigned short* __restrict__ leaf,
+                                                              const double* __restrict__ leaf_values, int num_leaves,
+                                                              double scale, double bias, double* __restrict__ score,
+                                                              int n) {
+  extern __shared__ double s_val[];
+  for (int l = threadIdx.x; l < num_leaves; l += 256) s_val[l] = scale * leaf_values[l] + bias;
+  __syncthreads();
+  const int n4 = n >> 2;
+  for (int q = blockIdx.x * 256 + threadIdx.x; q < n4; q += gridDim.x * 256) {
+    const ushort4 l = reinterpret_cast<const ushort4*>(leaf)[q];
+    double2 a = reinterpret_cast<double2*>(score)[2 * q];
+    double2 b = reinterpret_cast<double2*>(score)[2 * q + 1];
+    if (l.x != 0xFFFF) a.x += s_val[l.x];
+    if (l.y != 0xFFFF) a.y += s_val[l.y];
+    if (l.z != 0xFFFF) b.x += s_val[l.z];
+    if (l.w != 0xFFFF) b.y += s_val[l.w];
+    reinterpret_cast<double2*>(score)[2 * q] = a;
+    reinterpret_cast<double2*>(score)[2 * q + 1] = b;
+  }
+  if (blockIdx.x == 0) {
+    for (int i = (n4 << 2) + threadIdx.x; i < n; i += 256) {
+      const unsigned short l = leaf[i];
+      if (l != 0xFFFF) score[i] += s_val[l];
+    }
+  }
+}
+
 __global__ void __launch_bounds__(256) leaf_assign_kernel(LearnerDev d, int* __restrict__ out) {
   const TreeState& t = *d.ts;
   const int U = t.seg_units, S = t.num_segments;
@@ -431,8 +476,17 @@ void launch_partition(const LearnerDev& d, cudaStream_t s) {
 }
 
 void launch_add_score(const LearnerDev& d, const double* leaf_values_dev, double scale, double bias, double* score,
-                      cudaStream_t s) {
-  GBL_LAUNCH(add_score_kernel, kPartGrid, 256, 0, s, d, leaf_values_dev, scale, bias, score);
+                      unsigned short* leaf_scratch, bool partial_rows, cudaStream_t s) {
+  const int nl = d.p.num_leaves;
+  // the streaming pass wants a 16-byte aligned score vector; anything else takes the scattered update
+  if (leaf_scratch == nullptr || nl > 4096 || (reinterpret_cast<uintptr_t>(score) & 15) != 0) {
+    GBL_LAUNCH(add_score_kernel, kPartGrid, 256, 0, s, d, leaf_values_dev, scale, bias, score);
+    return;
+  }
+  if (partial_rows) GBL_CUDA(cudaMemsetAsync(leaf_scratch, 0xFF, sizeof(unsigned short) * d.num_data, s));
+  GBL_LAUNCH(leaf_mark_kernel, kPartGrid, 256, 0, s, d, leaf_scratch);
+  GBL_LAUNCH(add_score_dense_kernel, kNumSM * 8, 256, sizeof(double) * nl, s, leaf_scratch, leaf_values_dev, nl, scale, bias,
+             score, d.num_data);
 }
 
 void launch_leaf_assignment(const LearnerDev& d, int* out, cudaStream_t s) {
