@@ -169,6 +169,14 @@ GBL_API int gbl_learner_reset_config(gbl_learner* learner, const gbl_learner_con
 GBL_API int gbl_learner_set_feature_mask(gbl_learner* learner, const int8_t* is_feature_used_host);
 /* TreeLearner::SetBaggingData (tree_learner.h:75): sorted row subset used for the next trees; NULL/0 = all rows */
 GBL_API int gbl_learner_set_bagging_data(gbl_learner* learner, const int32_t* used_indices_host, int32_t num_used);
+/* BaggingSampleStrategy::Bagging (src/boosting/bagging.hpp:31-139) drawn ON THE DEVICE: every block of 1024 rows owns
+ * a generator seeded bagging_seed + block whose state persists between calls (reset != 0 or a new seed re-seeds),
+ * each row of the block draws NextFloat() and joins the bag below bagging_fraction -- the reference's integers, so the
+ * bag equals the reference's whatever its thread count.  Replaces the per-iteration host draw + index upload of
+ * gbl_learner_set_bagging_data; the bag size is returned (it is read back, 8 bytes).  A bag that happens to hold every
+ * row trains on every row.  Same restrictions as gbl_learner_set_bagging_data. */
+GBL_API int gbl_learner_bagging_dev(gbl_learner* learner, int32_t bagging_seed, double bagging_fraction, int32_t reset,
+                                    int32_t* out_bag_count);
 /* GradientDiscretizer's host-generated uniform [0,1) arrays for stochastic rounding
  * (src/treelearner/gradient_discretizer.cpp:16-41) and the per-iteration start offset (:116).  */
 GBL_API int gbl_learner_set_quant_random(gbl_learner* learner, const double* grad_random_host,

@@ -81,7 +81,7 @@ EXPORTED_SYMBOLS = [
     "gbl_dataset_get_feature_bins", "gbl_dataset_get_feature_bins_rowmajor",
     "gbl_comm_get_unique_id", "gbl_comm_create", "gbl_comm_free", "gbl_comm_allreduce_host_f64", "gbl_comm_info",
     "gbl_learner_create", "gbl_learner_free", "gbl_learner_reset_config", "gbl_learner_set_feature_mask",
-    "gbl_learner_set_bagging_data", "gbl_learner_set_quant_random", "gbl_learner_set_quant_random_start",
+    "gbl_learner_set_bagging_data", "gbl_learner_bagging_dev", "gbl_learner_set_quant_random", "gbl_learner_set_quant_random_start",
     "gbl_learner_train", "gbl_learner_train_host", "gbl_learner_train_async", "gbl_learner_train_finish",
     "gbl_learner_add_prediction_to_score", "gbl_learner_add_prediction_to_score_dev",
     "gbl_learner_add_prediction_out_of_bag_dev", "gbl_learner_add_prediction_to_dataset_dev", "gbl_learner_get_leaf_values", "gbl_learner_get_leaf_assignment", "gbl_learner_get_leaf_indices", "gbl_learner_get_histogram",
@@ -310,6 +310,13 @@ class Learner:
         else:
             a = np.ascontiguousarray(indices, dtype=np.int32)
             check(lib().gbl_learner_set_bagging_data(self.handle, _ptr(a), ctypes.c_int32(len(a))))
+
+    def bagging_dev(self, seed, fraction, reset=False):
+        """Draws the reference's bag on the device (gbl_learner_bagging_dev); returns the bag size."""
+        out = ctypes.c_int32(0)
+        check(lib().gbl_learner_bagging_dev(self.handle, ctypes.c_int32(seed), ctypes.c_double(fraction),
+                                            ctypes.c_int32(1 if reset else 0), ctypes.byref(out)))
+        return out.value
 
     def set_quant_random(self, rg, rh):
         rg = np.ascontiguousarray(rg, dtype=np.float64)

@@ -88,7 +88,12 @@ __host__ __device__ inline int child_buf(int buf) { return buf == 2 ? 0 : (buf ^
 void launch_iota(int* out, int n, cudaStream_t s);
 void launch_build_records(uint8_t* rec, int rec_stride, int tile_stride, const uint8_t* row_bins, int row_stride, int n,
                           cudaStream_t s);
-void launch_tree_begin(const LearnerDev& d, const int* bag_indices, int bag_count, cudaStream_t s);
+// bag_count_dev != nullptr: the bag size is read on the device (device-drawn bags change size without a new graph)
+void launch_tree_begin(const LearnerDev& d, const int* bag_indices, int bag_count, const int* bag_count_dev, cudaStream_t s);
+// bagging.cu
+void launch_bag_seed(unsigned* state, int nblk, int seed, cudaStream_t s);
+void launch_bag_draw(unsigned* state, int nblk, int n, double fraction, unsigned* bits, int* blk_cnt, int* blk_off,
+                     int* counts, int* bag, int* oob, cudaStream_t s);
 void launch_maxabs(const LearnerDev& d, cudaStream_t s);
 void launch_scales_and_convert(const LearnerDev& d, cudaStream_t s);
 

@@ -60,6 +60,16 @@ struct Learner {
   int bag_count = 0;
   int* oob_indices = nullptr;  // rows outside the bag (complement of bag_indices)
   int oob_count = 0;
+  // device-drawn bags (gbl_learner_bagging_dev): per-block generator states, 1 bit per row, block counts / offsets,
+  // {bag size, out-of-bag size} on the device and in pinned host memory
+  bool bag_on_device = false;
+  unsigned* bag_state = nullptr;
+  unsigned* bag_bits = nullptr;
+  int* bag_blk_cnt = nullptr;
+  int* bag_blk_off = nullptr;
+  int* bag_counts_dev = nullptr;
+  int* bag_counts_pinned = nullptr;
+  int bag_seed = 0;
   float* grad_stage = nullptr;  // train_host staging
   float* hess_stage = nullptr;
   long long* tap_hist = nullptr;
@@ -374,6 +384,12 @@ static void learner_free(Learner* L) {
   cudaFree(L->rand_h);
   cudaFree(L->bag_indices);
   cudaFree(L->oob_indices);
+  cudaFree(L->bag_state);
+  cudaFree(L->bag_bits);
+  cudaFree(L->bag_blk_cnt);
+  cudaFree(L->bag_blk_off);
+  cudaFree(L->bag_counts_dev);
+  if (L->bag_counts_pinned) cudaFreeHost(L->bag_counts_pinned);
   cudaFree(L->grad_stage);
   cudaFree(L->hess_stage);
   cudaFree(L->tap_hist);
@@ -395,7 +411,7 @@ static void enqueue_prologue(Learner* L, cudaStream_t s, cudaGraphConditionalHan
   {
     StageTimer tm(L, s, kStageOther);
     GBL_CUDA(cudaMemsetAsync(L->hist_pool, 0, sizeof(long long) * d.slot_stride, s));  // slot 0; later slots: part_scatter
-    launch_tree_begin(d, L->bag_indices, L->bag_count, s);
+    launch_tree_begin(d, L->bag_indices, L->bag_count, L->bag_on_device ? L->bag_counts_dev : nullptr, s);
     launch_maxabs(d, s);
   }
   if (multi) {
@@ -568,7 +584,7 @@ static void train_async(Learner* L, const float* grad_dev, const float* hess_dev
   if (L->use_graph && !multi && !L->profiling) {
     const bool stale = L->graph_exec == nullptr || L->graph_grad != grad_dev || L->graph_hess != hess_dev ||
                        L->graph_rand_start != d.rand_start || L->graph_bag != L->bag_indices ||
-                       L->graph_bag_count != L->bag_count;
+                       L->graph_bag_count != (L->bag_on_device ? -2 : L->bag_count);
     if (stale) {
       drop_graph(L);
       const long long launches_before = g_kernel_launches.load();
@@ -578,7 +594,7 @@ static void train_async(Learner* L, const float* grad_dev, const float* hess_dev
       L->graph_hess = hess_dev;
       L->graph_rand_start = d.rand_start;
       L->graph_bag = L->bag_indices;
-      L->graph_bag_count = L->bag_count;
+      L->graph_bag_count = L->bag_on_device ? -2 : L->bag_count;  // device-drawn bags: the size is read on the device
     }
     GBL_CUDA(cudaGraphLaunch(L->graph_exec, L->stream));
     L->tree_in_graph = true;
@@ -731,6 +747,7 @@ int gbl_learner_set_bagging_data(gbl_learner* learner, const int32_t* used_indic
   DeviceGuard guard(L->ds->device);
   GBL_CUDA(cudaStreamSynchronize(L->stream));
   drop_graph(L);
+  L->bag_on_device = false;
   if (used_indices_host == nullptr || num_used <= 0 || num_used >= L->ds->num_data) {
     cudaFree(L->bag_indices);
     cudaFree(L->oob_indices);
@@ -761,6 +778,48 @@ int gbl_learner_set_bagging_data(gbl_learner* learner, const int32_t* used_indic
     GBL_CUDA(cudaMemcpy(L->oob_indices, oob.data(), sizeof(int) * oob.size(), cudaMemcpyHostToDevice));
     L->oob_count = static_cast<int>(oob.size());
   }
+  GBL_API_END();
+}
+
+int gbl_learner_bagging_dev(gbl_learner* learner, int32_t bagging_seed, double bagging_fraction, int32_t reset,
+                            int32_t* out_bag_count) {
+  GBL_API_BEGIN();
+  Learner* L = LEARNER(learner);
+  if (L == nullptr) fatal("gbl_learner_bagging_dev: null learner");
+  if (!(bagging_fraction > 0.0 && bagging_fraction <= 1.0)) fatal("gbl_learner_bagging_dev: bagging_fraction must be in (0, 1]");
+  if (L->comm != nullptr && L->comm->num_ranks > 1) fatal("learner: bagging with the data-parallel learner is not supported");
+  if (L->cfg.use_quantized_grad) fatal("learner: bagging with use_quantized_grad is not supported");
+  DeviceGuard guard(L->ds->device);
+  const int n = static_cast<int>(L->ds->num_data);
+  const int nblk = (n + 1023) / 1024;
+  if (L->bag_state == nullptr) {
+    GBL_CUDA(cudaMalloc(&L->bag_state, sizeof(unsigned) * nblk));
+    GBL_CUDA(cudaMalloc(&L->bag_bits, sizeof(unsigned) * nblk * 32));
+    GBL_CUDA(cudaMalloc(&L->bag_blk_cnt, sizeof(int) * nblk));
+    GBL_CUDA(cudaMalloc(&L->bag_blk_off, sizeof(int) * nblk));
+    GBL_CUDA(cudaMalloc(&L->bag_counts_dev, sizeof(int) * 2));
+    GBL_CUDA(cudaMallocHost(&L->bag_counts_pinned, sizeof(int) * 2));
+    reset = 1;
+  }
+  if (!L->bag_on_device || L->bag_indices == nullptr || L->oob_indices == nullptr) {
+    // first device-drawn bag (or after a host-provided one): the captured tree must read the bag size on the device
+    GBL_CUDA(cudaStreamSynchronize(L->stream));
+    drop_graph(L);
+    if (L->bag_indices == nullptr) GBL_CUDA(cudaMalloc(&L->bag_indices, sizeof(int) * n));
+    if (L->oob_indices == nullptr) GBL_CUDA(cudaMalloc(&L->oob_indices, sizeof(int) * n));
+    L->bag_on_device = true;
+  }
+  if (reset || bagging_seed != L->bag_seed) {
+    launch_bag_seed(L->bag_state, nblk, bagging_seed, L->stream);
+    L->bag_seed = bagging_seed;
+  }
+  launch_bag_draw(L->bag_state, nblk, n, bagging_fraction, L->bag_bits, L->bag_blk_cnt, L->bag_blk_off, L->bag_counts_dev,
+                  L->bag_indices, L->oob_indices, L->stream);
+  GBL_CUDA(cudaMemcpyAsync(L->bag_counts_pinned, L->bag_counts_dev, sizeof(int) * 2, cudaMemcpyDeviceToHost, L->stream));
+  GBL_CUDA(cudaStreamSynchronize(L->stream));
+  L->bag_count = L->bag_counts_pinned[0];
+  L->oob_count = L->bag_counts_pinned[1];
+  if (out_bag_count != nullptr) *out_bag_count = L->bag_count;
   GBL_API_END();
 }
 

@@ -12,15 +12,19 @@ __global__ void __launch_bounds__(256) iota_kernel(int* __restrict__ out, int n)
   if (i < n) out[i] = i;
 }
 
-__global__ void __launch_bounds__(256) copy_int_kernel(int* __restrict__ out, const int* __restrict__ in, int n) {
+__global__ void __launch_bounds__(256) copy_int_kernel(int* __restrict__ out, const int* __restrict__ in, int n,
+                                                       const int* __restrict__ n_dev) {
+  if (n_dev != nullptr) n = *n_dev;
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) out[i] = in[i];
 }
 
 // One CTA: resets the tree state for a new tree (SerialTreeLearner::BeforeTrain,
 // src/treelearner/serial_tree_learner.cpp:288-338) and sets the root up as the first wave's histogram job.
-__global__ void __launch_bounds__(256) tree_begin_kernel(LearnerDev d, int root_count, int root_buf) {
+__global__ void __launch_bounds__(256) tree_begin_kernel(LearnerDev d, int root_count, int root_buf,
+                                                         const int* __restrict__ root_count_dev) {
   const int tid = threadIdx.x;
+  if (root_count_dev != nullptr) root_count = *root_count_dev;
   for (int l = tid; l < d.p.num_leaves; l += blockDim.x) {
     d.leaf_values[l] = 0.0;
     d.leaf_node[l] = l == 0 ? 0 : -1;
@@ -171,12 +175,15 @@ void launch_iota(int* out, int n, cudaStream_t s) {
   GBL_LAUNCH(iota_kernel, (n + 255) / 256, 256, 0, s, out, n);
 }
 
-void launch_tree_begin(const LearnerDev& d, const int* bag_indices, int bag_count, cudaStream_t s) {
+void launch_tree_begin(const LearnerDev& d, const int* bag_indices, int bag_count, const int* bag_count_dev,
+                       cudaStream_t s) {
   const int root_count = bag_indices != nullptr ? bag_count : d.num_data;
+  if (bag_indices == nullptr) bag_count_dev = nullptr;
   // without bagging the root's segment is the learner's constant 0..N-1 buffer: nothing to initialise per tree
-  GBL_LAUNCH(tree_begin_kernel, 1, 256, 0, s, d, root_count, bag_indices != nullptr ? 0 : 2);
+  GBL_LAUNCH(tree_begin_kernel, 1, 256, 0, s, d, root_count, bag_indices != nullptr ? 0 : 2, bag_count_dev);
   if (bag_indices != nullptr) {
-    GBL_LAUNCH(copy_int_kernel, (bag_count + 255) / 256, 256, 0, s, d.idx[0], bag_indices, bag_count);
+    const int cap = bag_count_dev != nullptr ? d.num_data : bag_count;
+    GBL_LAUNCH(copy_int_kernel, (cap + 255) / 256, 256, 0, s, d.idx[0], bag_indices, bag_count, bag_count_dev);
   }
 }
 

@@ -102,16 +102,28 @@ void GBDT::Init(const Config* config, const Dataset* train_data, ObjectiveFuncti
 void GBDT::Bagging(int iter) {
   const bool enabled = config_->bagging_freq > 0 && config_->bagging_fraction < 1.0;
   if (!enabled) return;
+  B200TreeLearner* bl = dynamic_cast<B200TreeLearner*>(tree_learner_.get());
   constexpr int kBlock = 1024;  // bagging_rand_block_
-  if (bagging_rands_.empty()) {
+  if (!bagging_ready_) {
     // ResetSampleConfig (bagging.hpp:139-201)
+    bagging_ready_ = true;
     bag_data_cnt_ = static_cast<data_size_t>(config_->bagging_fraction * num_data_);
-    bag_data_indices_.resize(num_data_);
-    for (int i = 0; i < (num_data_ + kBlock - 1) / kBlock; ++i) bagging_rands_.emplace_back(config_->bagging_seed + i);
+    if (bl == nullptr) {
+      bag_data_indices_.resize(num_data_);
+      for (int i = 0; i < (num_data_ + kBlock - 1) / kBlock; ++i) bagging_rands_.emplace_back(config_->bagging_seed + i);
+    }
     need_re_bagging_ = true;
   }
   if (!((bag_data_cnt_ < num_data_ && iter % config_->bagging_freq == 0) || need_re_bagging_)) return;
+  const bool first = need_re_bagging_;
   need_re_bagging_ = false;
+  if (bl != nullptr) {
+    // the same draw on the device: one thread per block generator, compaction by a prefix scan; nothing but the
+    // bag size crosses PCIe
+    bag_data_cnt_ = bl->BaggingOnDevice(config_->bagging_seed, config_->bagging_fraction, first);
+    Log::Debug("Re-bagging, using %d data to train", bag_data_cnt_);
+    return;
+  }
   data_size_t cnt = 0;
   for (data_size_t i = 0; i < num_data_; ++i) {
     // bagging.hpp:233: `NextFloat() < config_->bagging_fraction` (float promoted to double)

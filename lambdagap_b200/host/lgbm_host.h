@@ -337,6 +337,8 @@ class B200TreeLearner : public TreeLearner {
   void SetBaggingData(const Dataset* subset, const data_size_t* used_indices, data_size_t num_data) override;
   void AddPredictionToScore(const Tree* tree, double* out_score) const override;
   gbl_learner* handle() const { return handle_; }
+  // BaggingSampleStrategy::Bagging drawn on the device (the reference's bag, bit for bit); returns the bag size
+  data_size_t BaggingOnDevice(int bagging_seed, double bagging_fraction, bool reset);
   // device-resident pipeline used by GBDT: enqueue the tree, update the scores from the leaf outputs that are
   // still on the device, and only then wait for the split records
   void TrainAsync(const score_t* gradients, const score_t* hessians);
@@ -390,8 +392,9 @@ class GBDT {
   double BoostFromAverage();
   // BaggingSampleStrategy::Bagging (src/boosting/bagging.hpp:31-139), row-level bagging
   void Bagging(int iter);
-  std::vector<Random> bagging_rands_;     // one generator per block of 1024 rows (bagging.hpp:170-174)
+  std::vector<Random> bagging_rands_;     // one generator per block of 1024 rows (bagging.hpp:170-174); host path only
   std::vector<data_size_t> bag_data_indices_;
+  bool bagging_ready_ = false;
   data_size_t bag_data_cnt_ = 0;
   bool need_re_bagging_ = false;
   gbl_comm* comm_ = nullptr;

@@ -119,6 +119,12 @@ void B200TreeLearner::SetBaggingData(const Dataset* /*subset*/, const data_size_
   GblCheck(gbl_learner_set_bagging_data(handle_, used_indices, num_data));
 }
 
+data_size_t B200TreeLearner::BaggingOnDevice(int bagging_seed, double bagging_fraction, bool reset) {
+  int32_t cnt = 0;
+  GblCheck(gbl_learner_bagging_dev(handle_, bagging_seed, bagging_fraction, reset ? 1 : 0, &cnt));
+  return cnt;
+}
+
 Tree* B200TreeLearner::Train(const score_t* gradients, const score_t* hessians, bool /*is_first_tree*/) {
   TrainAsync(gradients, hessians);
   return FinishTrain();

@@ -189,3 +189,58 @@ def test_packed_columns_round_trip(gpu):
     sub_cols = [cols[f] for f in keep]
     prof, ns = _compare(sub_infos, sub_cols, g, h, True, dict(num_leaves=31, min_data_in_leaf=20))
     assert ns >= 5
+
+
+def _reference_bags(n, seed, fraction, rounds):
+    """BaggingSampleStrategy::BaggingHelper (src/boosting/bagging.hpp:224-243) restated with integers: one LCG per block
+    of 1024 rows (include/LightGBM/utils/random.h), state carried from round to round."""
+    nblk = (n + 1023) // 1024
+    x = (seed + np.arange(nblk, dtype=np.int64)).astype(np.uint32)
+    bags = []
+    for _ in range(rounds):
+        draws = np.zeros((nblk, 1024), dtype=np.float32)
+        for k in range(1024):
+            live = (np.arange(nblk) * 1024 + k) < n  # the last block draws only for the rows it has
+            nx = (x.astype(np.uint64) * np.uint64(214013) + np.uint64(2531011)).astype(np.uint32)
+            x = np.where(live, nx, x)
+            draws[:, k] = ((x >> np.uint32(16)) & np.uint32(0x7FFF)).astype(np.float32) / np.float32(32768.0)
+        flat = draws.reshape(-1)[:n]
+        bags.append(np.flatnonzero(flat.astype(np.float64) < fraction).astype(np.int32))
+    return bags
+
+
+def test_bagging_drawn_on_device(gpu):
+    """gbl_learner_bagging_dev draws the reference's bag (block-wise LCGs, state carried between calls) on the device:
+    the tree equals the one grown on the same bag handed over from the host, rows outside the bag belong to no leaf,
+    and the bag size changes from call to call without invalidating anything."""
+    n = 50000 + 333  # the last block of 1024 rows is partial
+    infos, cols, g, h = _data(32, n, 10, signal=1.5)
+    kw = dict(num_leaves=31, min_data_in_leaf=40)
+    seed, fraction = 7, 0.62
+    bags = _reference_bags(n, seed, fraction, 3)
+    assert len({len(b) for b in bags}) > 1
+    dds = capi.Dataset.from_bins(infos, cols)
+    dev = capi.Learner(dds, capi.learner_config(use_quantized_grad=0, stochastic_rounding=0, **kw))
+    host = capi.Learner(dds, capi.learner_config(use_quantized_grad=0, stochastic_rounding=0, **kw))
+    for rnd, bag in enumerate(bags):
+        assert dev.bagging_dev(seed, fraction) == len(bag)
+        host.set_bagging_data(bag)
+        res_d, recs_d = dev.train_host(g, h)
+        res_h, recs_h = host.train_host(g, h)
+        assert res_d["num_splits"] == res_h["num_splits"] > 5
+        for a, b in zip(recs_d, recs_h):
+            assert a == b, "round %d" % rnd
+        assign = dev.leaf_assignment()
+        np.testing.assert_array_equal(assign, host.leaf_assignment())
+        inside = np.zeros(n, dtype=bool)
+        inside[bag] = True
+        assert np.all(assign[inside] >= 0) and np.all(assign[~inside] == -1)
+    # re-seeding restarts the sequence
+    assert dev.bagging_dev(seed, fraction, reset=True) == len(bags[0])
+    # a fraction of 1 puts every row in the bag
+    assert dev.bagging_dev(seed, 1.0) == n
+    res, _ = dev.train_host(g, h)
+    assert np.all(dev.leaf_assignment() >= 0)
+    dev.free()
+    host.free()
+    dds.free()
