@@ -28,8 +28,18 @@ elif which == "mslr":
     n, f = X.shape
     params = "objective=lambdarank lambdarank_target=%s lambdarank_truncation_level=30 num_leaves=255 learning_rate=0.1" % (
         sys.argv[3] if len(sys.argv) > 3 else "ndcg")
+elif which == "higgs":
+    # the bench shape with extra parameters from the command line, e.g. "bagging_fraction=0.9 bagging_freq=1" or
+    # "metric=auc,binary_logloss" (then the training metrics are evaluated after every iteration and timed)
+    n, f = 10_500_000, 28
+    X = rng.normal(size=(n, f)).astype(np.float32)
+    X[:, 1] = np.exp(X[:, 1])
+    w = rng.normal(size=f)
+    y = (X @ w + rng.normal(size=n) > 0).astype(np.float32)
+    group = None
+    params = "objective=binary num_leaves=255 learning_rate=0.1 " + (sys.argv[3] if len(sys.argv) > 3 else "")
 else:
-    raise SystemExit("epsilon | mslr")
+    raise SystemExit("epsilon | mslr | higgs")
 print(which, X.shape, "gen %.1fs" % (time.time() - t0), flush=True)
 t0 = time.time()
 ds = engine.Dataset(X, y, group=group, params="max_bin=255 verbose=-1")
@@ -41,7 +51,12 @@ for it in range(iters):
     t0 = time.time()
     bst.update()
     dt = time.time() - t0
-    print("iter %d: %.2f ms" % (it, dt * 1e3), flush=True)
+    ev = ""
+    if "metric=" in params:
+        t1 = time.time()
+        vals = bst.eval(0)
+        ev = "  eval %s = %s in %.2f ms" % (bst.eval_names(), np.round(vals, 6), (time.time() - t1) * 1e3)
+    print("iter %d: %.2f ms%s" % (it, dt * 1e3, ev), flush=True)
 lrn.set_profiling(True)
 bst.update()
 print("profile", lrn.profile(reset=True))
