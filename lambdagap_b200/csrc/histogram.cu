@@ -145,6 +145,11 @@ struct QuantAcc {
 // Per batch of 32 rows and warp: 8 LDS.128 (row ids) + 32 LDG.U8 in flight together + 16 LDS.128 + 128 ATOMS.ADD.
 constexpr int kFloatFlushCap = 65536;
 
+// CONST_H: ObjectiveFunction::IsConstantHessian() (unweighted L2, regression_objective.hpp:152-158).  Every row has the
+// same fixed-point hessian, so the hessian planes are replaced by ONE count plane (3 ATOMS per cell instead of 4) and
+// the hessian sum of a bin is count * h_const at flush time -- the same integer the four-plane path accumulates.  The
+// reference takes the analogous short cut (count-only ConstructHistogram, dense_bin.hpp:124-127).
+template <bool CONST_H>
 struct FloatAcc {
   static constexpr int kPlanes = 4;
   static constexpr int kStageBytes = 16;
@@ -157,6 +162,7 @@ struct FloatAcc {
   const float* grad;
   const float* hess;
   double g_scale, h_scale;
+  long long h_const;  // CONST_H: the fixed-point hessian every row carries
   bool convert;
 
   __device__ __forceinline__ void accumulate(const int* __restrict__ indices, int r0, int r1, int warp, int lane) const {
@@ -193,6 +199,7 @@ struct FloatAcc {
         bins[4 * k + 2] = __ldg(rp + static_cast<size_t>(static_cast<unsigned>(rr.z)) * rs);
         bins[4 * k + 3] = __ldg(rp + static_cast<size_t>(static_cast<unsigned>(rr.w)) * rs);
       }
+      if (CONST_H) v.y = r >= 0 ? 1 : 0;  // the count plane's addend
       sv[lane] = v;
       __syncwarp();
 #pragma unroll
@@ -201,13 +208,21 @@ struct FloatAcc {
         const unsigned a = col + bins[2 * k] * (kTile * 4);
         red_shared_add(a, vv.x & 0xffff);
         red_shared_add(a + kPlane * 4, vv.x >> 16);
-        red_shared_add(a + 2 * kPlane * 4, vv.y & 0xffff);
-        red_shared_add(a + 3 * kPlane * 4, vv.y >> 16);
+        if (CONST_H) {
+          red_shared_add(a + 2 * kPlane * 4, vv.y);
+        } else {
+          red_shared_add(a + 2 * kPlane * 4, vv.y & 0xffff);
+          red_shared_add(a + 3 * kPlane * 4, vv.y >> 16);
+        }
         const unsigned b = col + bins[2 * k + 1] * (kTile * 4);
         red_shared_add(b, vv.z & 0xffff);
         red_shared_add(b + kPlane * 4, vv.z >> 16);
-        red_shared_add(b + 2 * kPlane * 4, vv.w & 0xffff);
-        red_shared_add(b + 3 * kPlane * 4, vv.w >> 16);
+        if (CONST_H) {
+          red_shared_add(b + 2 * kPlane * 4, vv.w);
+        } else {
+          red_shared_add(b + 2 * kPlane * 4, vv.w & 0xffff);
+          red_shared_add(b + 3 * kPlane * 4, vv.w >> 16);
+        }
       }
     }
   }
@@ -216,7 +231,9 @@ struct FloatAcc {
     for (int e = threadIdx.x; e < kPlane; e += kHistThreads) {
       const long long g = (static_cast<long long>(sh[e + kPlane]) << 16) + static_cast<long long>(static_cast<unsigned>(sh[e]));
       const long long h =
-          (static_cast<long long>(sh[e + 3 * kPlane]) << 16) + static_cast<long long>(static_cast<unsigned>(sh[e + 2 * kPlane]));
+          CONST_H ? static_cast<long long>(static_cast<unsigned>(sh[e + 2 * kPlane])) * h_const
+                  : (static_cast<long long>(sh[e + 3 * kPlane]) << 16) +
+                        static_cast<long long>(static_cast<unsigned>(sh[e + 2 * kPlane]));
       if ((e & 31) < lanes_used) {
         if (g != 0) atomicAdd(reinterpret_cast<unsigned long long*>(&dst[e].x), static_cast<unsigned long long>(g));
         if (h != 0) atomicAdd(reinterpret_cast<unsigned long long*>(&dst[e].y), static_cast<unsigned long long>(h));
@@ -224,7 +241,7 @@ struct FloatAcc {
       sh[e] = 0;
       sh[e + kPlane] = 0;
       sh[e + 2 * kPlane] = 0;
-      sh[e + 3 * kPlane] = 0;
+      if (!CONST_H) sh[e + 3 * kPlane] = 0;
     }
   }
 };
@@ -306,6 +323,7 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_quant_kernel(LearnerDev 
   hist_drive(d, acc, out, explicit_indices, explicit_count, flush_cap, 1);
 }
 
+template <bool CONST_H>
 __global__ void __launch_bounds__(kHistThreads, 1) hist_float_kernel(LearnerDev d, long long* __restrict__ out,
                                                                      const int* explicit_indices, int explicit_count) {
   extern __shared__ int sh[];
@@ -313,7 +331,7 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_float_kernel(LearnerDev 
   for (int e = threadIdx.x; e < 4 * kPlane; e += kHistThreads) sh[e] = 0;
   __syncthreads();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  FloatAcc acc;
+  FloatAcc<CONST_H> acc;
   acc.sh = sh;
   acc.sr = sh + 4 * kPlane + warp * 128;
   acc.sv = reinterpret_cast<int2*>(acc.sr + 32);
@@ -325,6 +343,9 @@ __global__ void __launch_bounds__(kHistThreads, 1) hist_float_kernel(LearnerDev 
   acc.hess = d.hess;
   acc.g_scale = d.ts->g_scale;
   acc.h_scale = d.ts->h_scale;
+  // every row's hessian is hess[0] (the caller's IsConstantHessian contract, serial_tree_learner.cpp:63,
+  // dataset.cpp:1403-1406 multiplies the counts by hessians[0] the same way)
+  acc.h_const = CONST_H ? static_cast<long long>(__double2int_rn(static_cast<double>(d.hess[0]) * acc.h_scale)) : 0;
   // the first pass of a tree also converts the gradients (to_fixed: exact power-of-two fixed point, |value| <= 2^30);
   // with several tiles every tile block of a record carries its own copy of the pair, written by that tile's CTAs
   acc.convert = explicit_count < 0 && d.ts->waves == 0;
@@ -335,7 +356,8 @@ static const int kSmemQ = kPlane * 4 + kHistWarps * 32 * 8;        // 32 KB + 8 
 static const int kSmemF = 4 * kPlane * 4 + kHistWarps * 32 * 16;   // 128 KB + 16 KB staging
 
 void histogram_setup() {
-  GBL_CUDA(cudaFuncSetAttribute(hist_float_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemF));
+  GBL_CUDA(cudaFuncSetAttribute(hist_float_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemF));
+  GBL_CUDA(cudaFuncSetAttribute(hist_float_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemF));
   GBL_CUDA(cudaFuncSetAttribute(hist_quant_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemQ));
 }
 
@@ -351,8 +373,11 @@ void launch_histogram(const LearnerDev& d, const int* explicit_indices, int expl
     flush_cap = std::max(256, std::min(flush_cap, 1 << 20));
     GBL_LAUNCH(hist_quant_kernel, dim3(gx, tiles), kHistThreads, kSmemQ, s, d, explicit_out, explicit_indices,
                explicit_count, flush_cap);
+  } else if (d.p.is_constant_hessian) {
+    GBL_LAUNCH(hist_float_kernel<true>, dim3(gx, tiles), kHistThreads, kSmemF, s, d, explicit_out, explicit_indices,
+               explicit_count);
   } else {
-    GBL_LAUNCH(hist_float_kernel, dim3(gx, tiles), kHistThreads, kSmemF, s, d, explicit_out, explicit_indices,
+    GBL_LAUNCH(hist_float_kernel<false>, dim3(gx, tiles), kHistThreads, kSmemF, s, d, explicit_out, explicit_indices,
                explicit_count);
   }
 }
