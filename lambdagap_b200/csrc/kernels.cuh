@@ -4,8 +4,21 @@
 
 namespace gbl {
 
+// Peer-memory exchange of the data-parallel learner (exchange.cu); all null on one GPU.
+struct PeerX {
+  long long* const* pool;   // [num_ranks] every rank's histogram pool (own pool at [rank]), mapped through CUDA IPC
+  unsigned* const* flags;   // [num_ranks] every rank's barrier flag array ([num_ranks] words each)
+  float* const* maxbuf;     // [num_ranks] every rank's (max |g|, max |h|) deposit array ([num_ranks][2] floats each)
+  unsigned* epoch;          // own barrier sequence number
+  unsigned* dead;           // own sticky "a barrier timed out" flag
+  int rank;
+  int pad;
+  long long timeout_cycles;  // bound of every barrier wait (SM clocks)
+};
+
 // Everything a per-tree kernel needs to find its inputs; passed by value (fits the 4 KB parameter space).
 struct LearnerDev {
+  PeerX px;
   // dataset
   const uint8_t* col_bins;
   uint8_t* rec;            // learner-owned row records: [row][32 bins per tile ...][gradient pair], see learner.cu
@@ -90,6 +103,10 @@ void launch_build_records(uint8_t* rec, int rec_stride, int tile_stride, const u
                           cudaStream_t s);
 // bag_count_dev != nullptr: the bag size is read on the device (device-drawn bags change size without a new graph)
 void launch_tree_begin(const LearnerDev& d, const int* bag_indices, int bag_count, const int* bag_count_dev, cudaStream_t s);
+// exchange.cu
+void launch_xchg_barrier(const LearnerDev& d, cudaStream_t s);
+void launch_xchg_reduce(const LearnerDev& d, int is_root, cudaStream_t s);
+void launch_xchg_max(const LearnerDev& d, cudaStream_t s);
 // bagging.cu
 void launch_bag_seed(unsigned* state, int nblk, int seed, cudaStream_t s);
 void launch_bag_draw(unsigned* state, int nblk, int n, double fraction, unsigned* bits, int* blk_cnt, int* blk_off,

@@ -60,6 +60,12 @@ struct Learner {
   int bag_count = 0;
   int* oob_indices = nullptr;  // rows outside the bag (complement of bag_indices)
   int oob_count = 0;
+  // peer-memory exchange of the data-parallel learner (exchange.cu): control block, device pointer tables, mapped peers
+  bool peer = false;
+  unsigned char* xchg_ctl = nullptr;     // own: flags[R] | maxbuf[R][2] | epoch | dead
+  void** xchg_tables = nullptr;          // device: pool[R] | flags[R] | maxbuf[R]
+  std::vector<void*> peer_pool_maps;     // cudaIpcOpenMemHandle results (other ranks only)
+  std::vector<void*> peer_ctl_maps;
   // device-drawn bags (gbl_learner_bagging_dev): per-block generator states, 1 bit per row, block counts / offsets,
   // {bag size, out-of-bag size} on the device and in pinned host memory
   bool bag_on_device = false;
@@ -162,6 +168,9 @@ static LearnerParams make_params(const Learner* L) {
   p.path_smooth = c.path_smooth;
   return p;
 }
+
+static void setup_peer(Learner* L);
+static void teardown_peer(Learner* L);
 
 static void drop_graph(Learner* L) {
   if (L->graph_exec != nullptr) {
@@ -363,6 +372,7 @@ static Learner* learner_create(const Dataset* ds, const gbl_learner_config* cfg,
   alloc_tree_buffers(L);
   build_records(L);
   histogram_setup();
+  setup_peer(L);
   return L;
 }
 
@@ -371,6 +381,7 @@ static void learner_free(Learner* L) {
   DeviceGuard guard(L->ds->device);
   cudaStreamSynchronize(L->stream);
   drop_graph(L);
+  teardown_peer(L);
   free_tree_buffers(L);
   cudaFree(L->ts);
   cudaFree(L->idx[0]);
@@ -403,6 +414,122 @@ static void learner_free(Learner* L) {
   delete L;
 }
 
+// ---- peer-memory exchange set-up (data-parallel learner, one process per GPU).  Collective: every rank calls it at the
+// same point (learner creation / reset_config).  Handles travel through one int64 all-reduce (each rank fills its own
+// 128 bytes of a zeroed table).  If any rank cannot map a peer (ranks sharing one process, no peer access) all ranks
+// keep the NCCL path.
+constexpr size_t kCtlFlagsOff = 0, kCtlMaxOff = 256, kCtlEpochOff = 1024, kCtlDeadOff = 1028, kCtlBytes = 2048;
+
+static void teardown_peer(Learner* L) {
+  for (void* p : L->peer_pool_maps) cudaIpcCloseMemHandle(p);
+  for (void* p : L->peer_ctl_maps) cudaIpcCloseMemHandle(p);
+  L->peer_pool_maps.clear();
+  L->peer_ctl_maps.clear();
+  cudaFree(L->xchg_ctl);
+  cudaFree(L->xchg_tables);
+  L->xchg_ctl = nullptr;
+  L->xchg_tables = nullptr;
+  L->peer = false;
+  L->dev.px = PeerX{};
+}
+
+static void setup_peer(Learner* L) {
+  teardown_peer(L);
+  Comm* c = L->comm;
+  if (c == nullptr || c->num_ranks <= 1) return;
+  const int R = c->num_ranks, me = c->rank;
+  bool want = R <= 16 && !(L->cfg.use_quantized_grad && L->cfg.quant_train_renew_leaf);
+  if (const char* e = std::getenv("GBL_PEER_EXCHANGE")) want = want && std::atoi(e) != 0;
+  cudaStream_t s = L->stream;
+  GBL_CUDA(cudaMalloc(&L->xchg_ctl, kCtlBytes));
+  GBL_CUDA(cudaMemset(L->xchg_ctl, 0, kCtlBytes));
+  // 16 int64 words per rank: two 64-byte IPC handles (pool, control block)
+  long long* table_dev = nullptr;
+  GBL_CUDA(cudaMalloc(&table_dev, sizeof(long long) * 16 * R));
+  GBL_CUDA(cudaMemset(table_dev, 0, sizeof(long long) * 16 * R));
+  GBL_CUDA(cudaDeviceSynchronize());  // the control block is zero before any peer can learn its handle
+  cudaIpcMemHandle_t hp, hc;
+  bool ok = want;
+  if (ok && cudaIpcGetMemHandle(&hp, L->hist_pool) != cudaSuccess) ok = false;
+  if (ok && cudaIpcGetMemHandle(&hc, L->xchg_ctl) != cudaSuccess) ok = false;
+  cudaGetLastError();
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  if (ok) {
+    GBL_CUDA(cudaMemcpy(table_dev + 16 * me, &hp, 64, cudaMemcpyHostToDevice));
+    GBL_CUDA(cudaMemcpy(table_dev + 16 * me + 8, &hc, 64, cudaMemcpyHostToDevice));
+  }
+  comm_allreduce_i64(c, table_dev, static_cast<size_t>(16) * R, RedOp::kSum, s);
+  GBL_CUDA(cudaStreamSynchronize(s));
+  std::vector<long long> table(static_cast<size_t>(16) * R);
+  GBL_CUDA(cudaMemcpy(table.data(), table_dev, sizeof(long long) * table.size(), cudaMemcpyDeviceToHost));
+  cudaFree(table_dev);
+  std::vector<void*> pools(R, nullptr), ctls(R, nullptr);
+  pools[me] = L->hist_pool;
+  ctls[me] = L->xchg_ctl;
+  for (int r = 0; r < R && ok; ++r) {
+    if (r == me) continue;
+    cudaIpcMemHandle_t a, b;
+    std::memcpy(&a, &table[16 * r], 64);
+    std::memcpy(&b, &table[16 * r + 8], 64);
+    bool zero = true;
+    for (int k = 0; k < 16; ++k) zero = zero && table[16 * r + k] == 0;
+    if (zero) {  // that rank could not export its memory
+      ok = false;
+      break;
+    }
+    void* pp = nullptr;
+    void* pc = nullptr;
+    if (cudaIpcOpenMemHandle(&pp, a, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+      ok = false;
+      break;
+    }
+    L->peer_pool_maps.push_back(pp);
+    if (cudaIpcOpenMemHandle(&pc, b, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+      ok = false;
+      break;
+    }
+    L->peer_ctl_maps.push_back(pc);
+    pools[r] = pp;
+    ctls[r] = pc;
+  }
+  cudaGetLastError();
+  // unanimous or not at all
+  float* flag_dev = nullptr;
+  GBL_CUDA(cudaMalloc(&flag_dev, sizeof(float)));
+  const float mine = ok ? 0.f : 1.f;
+  GBL_CUDA(cudaMemcpy(flag_dev, &mine, sizeof(float), cudaMemcpyHostToDevice));
+  comm_allreduce_f32(c, flag_dev, 1, RedOp::kMax, s);
+  GBL_CUDA(cudaStreamSynchronize(s));
+  float any_failed = 1.f;
+  GBL_CUDA(cudaMemcpy(&any_failed, flag_dev, sizeof(float), cudaMemcpyDeviceToHost));
+  cudaFree(flag_dev);
+  if (any_failed != 0.f) {
+    teardown_peer(L);
+    return;
+  }
+  std::vector<void*> tables(static_cast<size_t>(3) * R);
+  for (int r = 0; r < R; ++r) {
+    tables[r] = pools[r];
+    tables[R + r] = static_cast<unsigned char*>(ctls[r]) + kCtlFlagsOff;
+    tables[2 * R + r] = static_cast<unsigned char*>(ctls[r]) + kCtlMaxOff;
+  }
+  GBL_CUDA(cudaMalloc(&L->xchg_tables, sizeof(void*) * tables.size()));
+  GBL_CUDA(cudaMemcpy(L->xchg_tables, tables.data(), sizeof(void*) * tables.size(), cudaMemcpyHostToDevice));
+  PeerX& x = L->dev.px;
+  x.pool = reinterpret_cast<long long* const*>(L->xchg_tables);
+  x.flags = reinterpret_cast<unsigned* const*>(L->xchg_tables + R);
+  x.maxbuf = reinterpret_cast<float* const*>(L->xchg_tables + 2 * R);
+  x.epoch = reinterpret_cast<unsigned*>(L->xchg_ctl + kCtlEpochOff);
+  x.dead = reinterpret_cast<unsigned*>(L->xchg_ctl + kCtlDeadOff);
+  x.rank = me;
+  double timeout_s = 60.0;
+  if (const char* e = std::getenv("GBL_PEER_TIMEOUT_S")) timeout_s = std::max(0.001, std::atof(e));
+  int khz = 1900000;
+  cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, L->ds->device);
+  x.timeout_cycles = static_cast<long long>(timeout_s * 1e3 * khz);
+  L->peer = true;
+}
+
 // ---- the three parts of a tree.  prologue: root histogram, root scan, first wave selected.  wave: split every
 // node of the wave, histograms of the smaller children, scan of all children, next wave selected.  epilogue: replay.
 static void enqueue_prologue(Learner* L, cudaStream_t s, cudaGraphConditionalHandle cond, int use_cond) {
@@ -418,7 +545,11 @@ static void enqueue_prologue(Learner* L, cudaStream_t s, cudaGraphConditionalHan
     // GradientDiscretizer: Network::GlobalSyncUpByMax (gradient_discretizer.cpp:101-104); also used for the
     // fixed-point scale in float mode so that every rank shares one scale.
     StageTimer tm(L, s, kStageComm);
-    comm_allreduce_f32(L->comm, &L->ts->max_abs_g, 2, RedOp::kMax, s);
+    if (L->peer) {
+      launch_xchg_max(d, s);
+    } else {
+      comm_allreduce_f32(L->comm, &L->ts->max_abs_g, 2, RedOp::kMax, s);
+    }
   }
   {
     StageTimer tm(L, s, kStageOther);
@@ -430,7 +561,13 @@ static void enqueue_prologue(Learner* L, cudaStream_t s, cudaGraphConditionalHan
   }
   if (multi) {
     StageTimer tm(L, s, kStageComm);
-    comm_allreduce_i64(L->comm, L->hist_pool, static_cast<size_t>(d.slot_stride), RedOp::kSum, s);
+    if (L->peer) {
+      launch_xchg_barrier(d, s);
+      launch_xchg_reduce(d, 1, s);
+      launch_xchg_barrier(d, s);
+    } else {
+      comm_allreduce_i64(L->comm, L->hist_pool, static_cast<size_t>(d.slot_stride), RedOp::kSum, s);
+    }
   }
   {
     StageTimer tm(L, s, kStageFind);
@@ -458,7 +595,13 @@ static void enqueue_wave_back(Learner* L, cudaStream_t s, cudaGraphConditionalHa
                               int num_slots) {
   const LearnerDev& d = L->dev;
   const bool multi = L->comm != nullptr && L->comm->num_ranks > 1;
-  if (multi && num_slots > 0) {
+  if (multi && L->peer) {
+    // the same sum over NVLink peer memory, sized on the device (exchange.cu): no host involvement, graph-capturable
+    StageTimer tm(L, s, kStageComm);
+    launch_xchg_barrier(d, s);
+    launch_xchg_reduce(d, 0, s);
+    launch_xchg_barrier(d, s);
+  } else if (multi && num_slots > 0) {
     // the wave's histograms + (smaller, larger) row counts in one all-reduce; replaces Network::ReduceScatter of
     // data_parallel_tree_learner.cpp:285-297 and the count sync of :457-458
     StageTimer tm(L, s, kStageComm);
@@ -581,7 +724,7 @@ static void train_async(Learner* L, const float* grad_dev, const float* hess_dev
   d.rand_h = d.rand_g != nullptr ? L->rand_h : nullptr;
   d.rand_start = L->rand_start;
   const bool multi = L->comm != nullptr && L->comm->num_ranks > 1;
-  if (L->use_graph && !multi && !L->profiling) {
+  if (L->use_graph && (!multi || L->peer) && !L->profiling) {
     const bool stale = L->graph_exec == nullptr || L->graph_grad != grad_dev || L->graph_hess != hess_dev ||
                        L->graph_rand_start != d.rand_start || L->graph_bag != L->bag_indices ||
                        L->graph_bag_count != (L->bag_on_device ? -2 : L->bag_count);
@@ -610,7 +753,9 @@ static void train_async(Learner* L, const float* grad_dev, const float* hess_dev
 // waves): prologue (tree_begin, [bagged index copy], maxabs, scales, histogram, root_init, scan, select) + 6 per
 // wave + the replay
 static long long kernels_of_tree(const Learner* L, const TreeState& t) {
-  return (L->bag_indices != nullptr ? 8 : 7) + 6LL * t.waves + 1 + ((L->cfg.use_quantized_grad && L->cfg.quant_train_renew_leaf) ? 3 : 0);
+  const long long xchg = L->peer ? 6 + 3LL * t.waves : 0;  // max exchange (3), root sum (3), 3 per wave
+  return (L->bag_indices != nullptr ? 8 : 7) + 6LL * t.waves + 1 + xchg +
+         ((L->cfg.use_quantized_grad && L->cfg.quant_train_renew_leaf) ? 3 : 0);
 }
 
 static void train_finish(Learner* L, gbl_tree_result* result, gbl_split_record* records) {
@@ -624,7 +769,8 @@ static void train_finish(Learner* L, gbl_tree_result* result, gbl_split_record* 
   if (t.error != 0)
     fatal("learner: internal error %d while growing the tree (%s)", t.error,
           t.error == 1 ? "the replay needed a node that was never expanded"
-                       : t.error == 2 ? "expansion capacity exhausted" : "a scan job was not reduced");
+                       : t.error == 2 ? "expansion capacity exhausted"
+                                      : t.error == 9 ? "a rank did not reach a peer-memory barrier in time" : "a scan job was not reduced");
   if (L->tree_in_graph) g_kernel_launches.fetch_add(kernels_of_tree(L, t), std::memory_order_relaxed);
   if (L->profiling) {
     for (size_t i = 0; i + 1 < L->ev_used; i += 2) {
@@ -712,6 +858,7 @@ int gbl_learner_reset_config(gbl_learner* learner, const gbl_learner_config* con
   drop_graph(L);
   const bool realloc = config->num_leaves != L->cfg.num_leaves || config->use_quantized_grad != L->cfg.use_quantized_grad;
   L->cfg = *config;
+  teardown_peer(L);
   if (realloc) {
     free_tree_buffers(L);
     alloc_tree_buffers(L);
@@ -720,6 +867,7 @@ int gbl_learner_reset_config(gbl_learner* learner, const gbl_learner_config* con
   } else {
     L->dev.p = make_params(L);
   }
+  setup_peer(L);  // collective: the ranks of a data-parallel learner reset their configuration together
   GBL_API_END();
 }
 
