@@ -13,10 +13,13 @@
 //     (row, tile) -- gather-friendly for sparse leaves, streaming for dense ones;
 //   * quantized mode: one ATOMS per cell on a packed (grad << 16) + hess word, flushed to HBM as the
 //     reference's packed int64 (grad << 32 | hess) with 64-bit RED atomics before the 16-bit halves can overflow;
-//   * float mode: gradients are exact power-of-two fixed point (|v| <= 2^30); each of grad/hess is one returning
-//     ATOMS on a low word plus a rare (|v| / 2^32) carry ATOMS on a high word -> exact 64-bit CTA partial sums,
-//     flushed with 64-bit RED atomics.  Sums are order-independent, so histograms are deterministic and
-//     identical for any grid shape or GPU count.
+//   * float mode: gradients are exact power-of-two fixed point (|v| <= 2^30) split into 16-bit limbs, one shared
+//     plane per limb (grad lo / hi, hess lo / hi): four non-returning ATOMS per cell, no carries, exact 64-bit CTA
+//     partial sums at flush time (64-bit RED atomics into the node's slot).  With a constant hessian (unweighted L2)
+//     the two hessian planes become one count plane: three ATOMS per cell.  Sums are order-independent, so histograms
+//     are deterministic and identical for any grid shape or GPU count;
+//   * memory-level parallelism: a warp requests the 32 bin sectors of a batch of 32 rows back to back and the
+//     gradient words alongside, with the next batch's row ids already in flight;
 //   * one launch serves a whole wave: the rows of all nodes whose histogram is due are cut into units of kHistUnit
 //     rows; every CTA takes a contiguous run of units, accumulates node by node in shared memory and flushes each
 //     node's partial sums to that node's slot.
