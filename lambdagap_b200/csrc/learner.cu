@@ -876,14 +876,20 @@ int gbl_learner_set_feature_mask(gbl_learner* learner, const int8_t* is_feature_
   Learner* L = LEARNER(learner);
   if (L == nullptr) fatal("gbl_learner_set_feature_mask: null learner");
   DeviceGuard guard(L->ds->device);
-  GBL_CUDA(cudaStreamSynchronize(L->stream));
-  drop_graph(L);
-  if (is_feature_used_host == nullptr) {
-    cudaFree(L->feature_mask);
-    L->feature_mask = nullptr;
+  if (is_feature_used_host != nullptr && L->feature_mask != nullptr) {
+    // a new mask in the same buffer (ColSampler::ResetByTree before every tree): ordered behind the previous tree on the
+    // learner's stream, and the captured tree stays valid because it reads the mask through the same pointer
+    GBL_CUDA(cudaMemcpyAsync(L->feature_mask, is_feature_used_host, L->ds->num_features, cudaMemcpyHostToDevice, L->stream));
   } else {
-    if (L->feature_mask == nullptr) GBL_CUDA(cudaMalloc(&L->feature_mask, L->ds->num_features));
-    GBL_CUDA(cudaMemcpy(L->feature_mask, is_feature_used_host, L->ds->num_features, cudaMemcpyHostToDevice));
+    GBL_CUDA(cudaStreamSynchronize(L->stream));
+    drop_graph(L);
+    if (is_feature_used_host == nullptr) {
+      cudaFree(L->feature_mask);
+      L->feature_mask = nullptr;
+    } else {
+      GBL_CUDA(cudaMalloc(&L->feature_mask, L->ds->num_features));
+      GBL_CUDA(cudaMemcpy(L->feature_mask, is_feature_used_host, L->ds->num_features, cudaMemcpyHostToDevice));
+    }
   }
   GBL_API_END();
 }

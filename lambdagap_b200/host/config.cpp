@@ -158,6 +158,8 @@ void Config::Set(const std::string& parameters) {
     const int int_max = std::numeric_limits<int16_t>::max();
     data_random_seed = next_short(0, int_max);
     bagging_seed = next_short(0, int_max);
+    next_short(0, int_max);  // drop_seed
+    feature_fraction_seed = next_short(0, int_max);
   }
 #define GET_INT(name) if (const std::string* v = get(#name)) name = std::stoi(*v)
 #define GET_DBL(name) if (const std::string* v = get(#name)) name = std::stod(*v)
@@ -185,6 +187,7 @@ void Config::Set(const std::string& parameters) {
   GET_DBL(neg_bagging_fraction);
   GET_BOOL(bagging_by_query);
   GET_DBL(feature_fraction);
+  GET_INT(feature_fraction_seed);
   GET_DBL(feature_fraction_bynode);
   GET_BOOL(extra_trees);
   GET_DBL(max_delta_step);
@@ -273,7 +276,8 @@ void Config::Set(const std::string& parameters) {
     Log::Fatal("device_type=%s: this library has no CPU path; use device_type=cuda", device_type.c_str());
   if (linear_tree) Log::Fatal("linear_tree is not supported by the B200 learner");
   if (extra_trees) Log::Fatal("extra_trees is not supported by the B200 learner");
-  if (feature_fraction < 1.0 || feature_fraction_bynode < 1.0) Log::Fatal("feature_fraction < 1 is not supported by the B200 learner");
+  if (feature_fraction_bynode < 1.0) Log::Fatal("feature_fraction_bynode < 1 is not supported by the B200 learner");
+  if (feature_fraction <= 0.0 || feature_fraction > 1.0) Log::Fatal("feature_fraction should be in (0.0, 1.0]");
   if (bagging_freq > 0 && bagging_fraction < 1.0) {
     if (use_quantized_grad)
       Log::Fatal("bagging with use_quantized_grad is not supported by the B200 learner (the reference's bagged quantized "

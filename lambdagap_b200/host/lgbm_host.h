@@ -72,6 +72,7 @@ struct Config {
   double neg_bagging_fraction = 1.0;
   bool bagging_by_query = false;
   double feature_fraction = 1.0;
+  int feature_fraction_seed = 2;
   double feature_fraction_bynode = 1.0;
   bool extra_trees = false;
   double max_delta_step = 0.0;
@@ -350,6 +351,15 @@ class B200TreeLearner : public TreeLearner {
  private:
   gbl_learner_config MakeConfig() const;
   void InitQuantRandom();
+  // ColSampler (src/treelearner/col_sampler.hpp:20-90), by-tree sampling: SetTrainingData / SetConfig / ResetByTree
+  void ColSamplerSetup(bool reseed);
+  void ColSamplerResetByTree();
+  Random col_random_{2};
+  int col_seed_ = 2;
+  std::vector<int> valid_feature_indices_;   // Dataset::ValidFeatureIndices(): real indices of the used features
+  std::vector<int8_t> is_feature_used_;      // per inner feature
+  int used_cnt_bytree_ = 0;
+  bool need_reset_bytree_ = false;
   const Config* config_;
   gbl_comm* comm_;
   const Dataset* train_data_ = nullptr;

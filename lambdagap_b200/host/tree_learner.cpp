@@ -100,6 +100,40 @@ void B200TreeLearner::Init(const Dataset* train_data, bool is_constant_hessian) 
   records_.resize(config_->num_leaves);
   quant_random_ready_ = false;
   if (config_->use_quantized_grad && config_->stochastic_rounding) InitQuantRandom();
+  ColSamplerSetup(true);  // SerialTreeLearner::Init -> col_sampler_.SetTrainingData (serial_tree_learner.cpp:59)
+}
+
+// ColSampler::SetTrainingData / SetConfig (col_sampler.hpp:39-75): the generator is created from
+// feature_fraction_seed once and re-created only when the seed changes; both end with one ResetByTree.
+void B200TreeLearner::ColSamplerSetup(bool reseed) {
+  if (reseed || col_seed_ != config_->feature_fraction_seed) {
+    col_seed_ = config_->feature_fraction_seed;
+    col_random_ = Random(col_seed_);
+  }
+  valid_feature_indices_.clear();
+  for (int i = 0; i < train_data_->num_features(); ++i) valid_feature_indices_.push_back(train_data_->RealFeatureIndex(i));
+  std::sort(valid_feature_indices_.begin(), valid_feature_indices_.end());
+  is_feature_used_.assign(train_data_->num_features(), 1);
+  const int total = static_cast<int>(valid_feature_indices_.size());
+  if (config_->feature_fraction >= 1.0f) {
+    need_reset_bytree_ = false;
+    used_cnt_bytree_ = total;
+    GblCheck(gbl_learner_set_feature_mask(handle_, nullptr));
+  } else {
+    need_reset_bytree_ = true;
+    // ColSampler::GetCnt: max(RoundInt(total * fraction), min(1, total))
+    used_cnt_bytree_ = std::max(static_cast<int>(total * config_->feature_fraction + 0.5f), std::min(1, total));
+  }
+  ColSamplerResetByTree();
+}
+
+// ColSampler::ResetByTree (col_sampler.hpp:77-90): Random::Sample picks used_cnt_bytree_ of the valid features
+void B200TreeLearner::ColSamplerResetByTree() {
+  if (!need_reset_bytree_) return;
+  std::fill(is_feature_used_.begin(), is_feature_used_.end(), 0);
+  const std::vector<int> used = col_random_.Sample(static_cast<int>(valid_feature_indices_.size()), used_cnt_bytree_);
+  for (int i : used) is_feature_used_[train_data_->InnerFeatureIndex(valid_feature_indices_[i])] = 1;
+  GblCheck(gbl_learner_set_feature_mask(handle_, is_feature_used_.data()));
 }
 
 void B200TreeLearner::ResetIsConstantHessian(bool is_constant_hessian) {
@@ -113,6 +147,7 @@ void B200TreeLearner::ResetConfig(const Config* config) {
   gbl_learner_config c = MakeConfig();
   GblCheck(gbl_learner_reset_config(handle_, &c));
   records_.resize(config_->num_leaves);
+  ColSamplerSetup(false);  // col_sampler_.SetConfig (serial_tree_learner.cpp:168)
 }
 
 void B200TreeLearner::SetBaggingData(const Dataset* /*subset*/, const data_size_t* used_indices, data_size_t num_data) {
@@ -131,6 +166,7 @@ Tree* B200TreeLearner::Train(const score_t* gradients, const score_t* hessians, 
 }
 
 void B200TreeLearner::TrainAsync(const score_t* gradients, const score_t* hessians) {
+  ColSamplerResetByTree();  // SerialTreeLearner::BeforeTrain (serial_tree_learner.cpp:293)
   if (quant_random_ready_) {
     GblCheck(gbl_learner_set_quant_random_start(handle_, quant_start_->dist(quant_start_->eng)));
   }

@@ -124,3 +124,21 @@ def test_example_lambdarank_conf(gpu):
               "min_data_in_leaf=50 min_sum_hessian_in_leaf=5.0")
     rb, ob = _train_both(X, y, params, 12, group=group)
     _compare_models(rb, ob, rtol=1e-5)
+
+
+@pytest.mark.parametrize("quant", [False, True])
+def test_feature_fraction_by_tree(gpu, quant):
+    """ColSampler::ResetByTree (src/treelearner/col_sampler.hpp:77-90): every tree sees the feature subset the reference
+    draws (Random::Sample with feature_fraction_seed, one draw at Init and one before every tree); the mask changes
+    from tree to tree without a new graph."""
+    X, y = H.make_binary(30000, 24, seed=23, nan_frac=0.03, zero_frac=0.2)
+    params = "objective=binary num_leaves=31 learning_rate=0.1 min_data_in_leaf=20 feature_fraction=0.6 feature_fraction_seed=11"
+    if quant:
+        params += " use_quantized_grad=true stochastic_rounding=false"
+    rb, ob = _train_both(X, y, params, 8)
+    _compare_models(rb, ob, rtol=1e-5)
+    used = {int(f) for t in R.parse_model_trees(ob.model_to_string()) for f in t["split_feature"]}
+    assert 8 <= len(used) <= 24
+    # the derived seed (seed -> feature_fraction_seed, src/io/config.cpp:257-268) and a small fraction
+    rb, ob = _train_both(X, y, "objective=binary num_leaves=15 seed=7 feature_fraction=0.2 min_data_in_leaf=20", 5)
+    _compare_models(rb, ob, rtol=1e-5)

@@ -143,7 +143,7 @@ def test_no_cpu_fallback_fails_loudly():
 
 
 def test_config_rejects_what_the_learner_does_not_implement():
-    for bad in ("boosting=dart", "linear_tree=true", "feature_fraction=0.5", "max_bin=1023", "device_type=cpu",
+    for bad in ("boosting=dart", "linear_tree=true", "feature_fraction_bynode=0.5", "max_bin=1023", "device_type=cpu",
                 "monotone_constraints=1,0", "tree_learner=voting"):
         with pytest.raises(engine.LightGBMError):
             engine.Dataset(np.zeros((10, 2), dtype=np.float32), np.zeros(10, dtype=np.float32), params=bad + " verbose=-1")
