@@ -418,7 +418,7 @@ static void learner_free(Learner* L) {
 // same point (learner creation / reset_config).  Handles travel through one int64 all-reduce (each rank fills its own
 // 128 bytes of a zeroed table).  If any rank cannot map a peer (ranks sharing one process, no peer access) all ranks
 // keep the NCCL path.
-constexpr size_t kCtlFlagsOff = 0, kCtlMaxOff = 256, kCtlEpochOff = 1024, kCtlDeadOff = 1028, kCtlBytes = 2048;
+constexpr size_t kCtlFlagsOff = 0, kCtlMaxOff = 256, kCtlEpochOff = 1024, kCtlDeadOff = 1028, kCtlBytes = 2048, kCtlAlloc = 2u << 20;
 
 static void teardown_peer(Learner* L) {
   for (void* p : L->peer_pool_maps) cudaIpcCloseMemHandle(p);
@@ -441,7 +441,9 @@ static void setup_peer(Learner* L) {
   bool want = R <= 16 && !(L->cfg.use_quantized_grad && L->cfg.quant_train_renew_leaf);
   if (const char* e = std::getenv("GBL_PEER_EXCHANGE")) want = want && std::atoi(e) != 0;
   cudaStream_t s = L->stream;
-  GBL_CUDA(cudaMalloc(&L->xchg_ctl, kCtlBytes));
+  // 2 MiB: an allocation of its own (small cudaMalloc blocks share a 2 MiB region, and one exported region can be
+  // mapped only once per peer process -- a second learner's control block in the same region could not be opened)
+  GBL_CUDA(cudaMalloc(&L->xchg_ctl, kCtlAlloc));
   GBL_CUDA(cudaMemset(L->xchg_ctl, 0, kCtlBytes));
   // 16 int64 words per rank: two 64-byte IPC handles (pool, control block)
   long long* table_dev = nullptr;
@@ -503,6 +505,9 @@ static void setup_peer(Learner* L) {
   float any_failed = 1.f;
   GBL_CUDA(cudaMemcpy(&any_failed, flag_dev, sizeof(float), cudaMemcpyDeviceToHost));
   cudaFree(flag_dev);
+  if (std::getenv("GBL_DEBUG_PEER") != nullptr)
+    std::fprintf(stderr, "[gbl] rank %d/%d: peer-memory exchange %s (wanted %d, mapped here %d)\n", me, R,
+                 any_failed != 0.f ? "OFF -> NCCL" : "on", want ? 1 : 0, ok ? 1 : 0);
   if (any_failed != 0.f) {
     teardown_peer(L);
     return;
