@@ -68,6 +68,19 @@ LGBM_B200_EXPORT int LGBM_BoosterGetEvalNames(BoosterHandle handle, const int le
                                               size_t* out_buffer_len, char** out_strs);
 LGBM_B200_EXPORT int LGBM_BoosterGetEval(BoosterHandle handle, int data_idx, int* out_len, double* out_results);
 
+/* include/LightGBM/c_api.h:747 -- learning_rate, num_leaves, min_data_in_leaf, regularisation, bagging / feature
+ * sampling parameters may change between iterations; objective, metric, boosting, device may not */
+LGBM_B200_EXPORT int LGBM_BoosterResetParameter(BoosterHandle handle, const char* parameters);
+/* include/LightGBM/c_api.h:756,828,904,1523,1551,1471 */
+LGBM_B200_EXPORT int LGBM_BoosterGetNumClasses(BoosterHandle handle, int* out_len);
+LGBM_B200_EXPORT int LGBM_BoosterNumModelPerIteration(BoosterHandle handle, int* out_tree_per_iteration);
+LGBM_B200_EXPORT int LGBM_BoosterGetNumFeature(BoosterHandle handle, int* out_len);
+LGBM_B200_EXPORT int LGBM_BoosterGetLeafValue(BoosterHandle handle, int tree_idx, int leaf_idx, double* out_val);
+LGBM_B200_EXPORT int LGBM_BoosterFeatureImportance(BoosterHandle handle, int num_iteration, int importance_type,
+                                                   double* out_results);
+LGBM_B200_EXPORT int LGBM_BoosterSaveModel(BoosterHandle handle, int start_iteration, int num_iteration,
+                                           int feature_importance_type, const char* filename);
+
 LGBM_B200_EXPORT int LGBM_BoosterGetCurrentIteration(BoosterHandle handle, int* out_iteration);
 LGBM_B200_EXPORT int LGBM_BoosterNumberOfTotalModel(BoosterHandle handle, int* out_models);
 /* src/c_api.cpp:2200,2209 */

@@ -21,6 +21,8 @@ LGBM_EXPORTED_SYMBOLS = [
     "LGBM_BoosterPredictForMat", "LGBM_BoosterSaveModelToString", "LGBM_NetworkGetNcclUniqueId",
     "LGBM_NetworkInitWithNccl", "LGBM_NetworkFree", "LGBM_BoosterGetTrainScoreRaw",
     "LGBM_DatasetCreateFromMatWithSample", "LGBM_BoosterGetLearnerHandle", "LGBM_B200_FindBin",
+    "LGBM_BoosterResetParameter", "LGBM_BoosterGetNumClasses", "LGBM_BoosterNumModelPerIteration",
+    "LGBM_BoosterGetNumFeature", "LGBM_BoosterGetLeafValue", "LGBM_BoosterFeatureImportance", "LGBM_BoosterSaveModel",
     "LGBM_BoosterAddValidData", "LGBM_BoosterGetEvalCounts", "LGBM_BoosterGetEvalNames", "LGBM_BoosterGetEval",
 ]
 
@@ -116,6 +118,26 @@ class Booster:
         _check(lib().LGBM_BoosterUpdateOneIterCustom(self.handle, grad.ctypes.data_as(ctypes.c_void_p),
                                                      hess.ctypes.data_as(ctypes.c_void_p), ctypes.byref(fin)))
         return fin.value
+
+    def reset_parameter(self, params):
+        _check(lib().LGBM_BoosterResetParameter(self.handle, ctypes.c_char_p(_params(params))))
+
+    def feature_importance(self, importance_type=0, num_iteration=-1):
+        n = ctypes.c_int(0)
+        _check(lib().LGBM_BoosterGetNumFeature(self.handle, ctypes.byref(n)))
+        out = np.zeros(n.value, dtype=np.float64)
+        _check(lib().LGBM_BoosterFeatureImportance(self.handle, ctypes.c_int(num_iteration), ctypes.c_int(importance_type),
+                                                   out.ctypes.data_as(ctypes.c_void_p)))
+        return out
+
+    def save_model(self, filename):
+        _check(lib().LGBM_BoosterSaveModel(self.handle, ctypes.c_int(0), ctypes.c_int(-1), ctypes.c_int(0),
+                                           ctypes.c_char_p(filename.encode())))
+
+    def leaf_value(self, tree_idx, leaf_idx):
+        out = ctypes.c_double(0)
+        _check(lib().LGBM_BoosterGetLeafValue(self.handle, ctypes.c_int(tree_idx), ctypes.c_int(leaf_idx), ctypes.byref(out)))
+        return out.value
 
     def add_valid(self, valid_set):
         """LGBM_BoosterAddValidData; `valid_set` must have been created with reference=<the training set>."""

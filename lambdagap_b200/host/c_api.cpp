@@ -1,6 +1,7 @@
 // c_api.cpp -- the reference's C API names for the hot-path subset (see include/lgbm_b200_c_api.h).
 // Reference: src/c_api.cpp (Booster class :169-195, :410-423; API_BEGIN/API_END :38-52).
 #include <algorithm>
+#include <cstdio>
 #include <cstring>
 #include <mutex>
 
@@ -198,6 +199,72 @@ int LGBM_BoosterGetEval(BoosterHandle handle, int data_idx, int* out_len, double
   const std::vector<double> res = b->boosting->GetEvalAt(data_idx);  // LGBM_BoosterGetEval (src/c_api.cpp:2200-2212)
   *out_len = static_cast<int>(res.size());
   for (size_t i = 0; i < res.size(); ++i) out_results[i] = res[i];
+  API_END();
+}
+
+int LGBM_BoosterResetParameter(BoosterHandle handle, const char* parameters) {
+  API_BEGIN();
+  Booster* b = reinterpret_cast<Booster*>(handle);
+  std::lock_guard<std::mutex> lock(b->mutex);
+  // Booster::ResetConfig (src/c_api.cpp:317-392): what may not change after the booster exists
+  const auto params = Config::Str2Map(parameters ? parameters : "");
+  if (params.count("num_class")) Log::Fatal("Cannot change num_class during training");
+  if (params.count("boosting")) Log::Fatal("Cannot change boosting during training");
+  if (params.count("metric")) Log::Fatal("Cannot change metric during training");
+  if (params.count("objective")) Log::Fatal("Cannot change objective during training (not supported by the B200 host layer)");
+  if (params.count("use_quantized_grad") || params.count("device_type") || params.count("tree_learner"))
+    Log::Fatal("Cannot change use_quantized_grad / device_type / tree_learner during training");
+  b->config.Set(parameters ? parameters : "");
+  b->boosting->ResetConfig(&b->config);
+  API_END();
+}
+
+int LGBM_BoosterGetNumClasses(BoosterHandle /*handle*/, int* out_len) {
+  API_BEGIN();
+  *out_len = 1;
+  API_END();
+}
+
+int LGBM_BoosterNumModelPerIteration(BoosterHandle /*handle*/, int* out_tree_per_iteration) {
+  API_BEGIN();
+  *out_tree_per_iteration = 1;
+  API_END();
+}
+
+int LGBM_BoosterGetNumFeature(BoosterHandle handle, int* out_len) {
+  API_BEGIN();
+  *out_len = reinterpret_cast<Booster*>(handle)->boosting->MaxFeatureIdx() + 1;
+  API_END();
+}
+
+int LGBM_BoosterGetLeafValue(BoosterHandle handle, int tree_idx, int leaf_idx, double* out_val) {
+  API_BEGIN();
+  Booster* b = reinterpret_cast<Booster*>(handle);
+  const auto& models = b->boosting->models();
+  if (tree_idx < 0 || tree_idx >= static_cast<int>(models.size())) Log::Fatal("tree_idx %d out of range", tree_idx);
+  if (leaf_idx < 0 || leaf_idx >= models[tree_idx]->num_leaves()) Log::Fatal("leaf_idx %d out of range", leaf_idx);
+  *out_val = models[tree_idx]->LeafOutput(leaf_idx);
+  API_END();
+}
+
+int LGBM_BoosterFeatureImportance(BoosterHandle handle, int num_iteration, int importance_type, double* out_results) {
+  API_BEGIN();
+  Booster* b = reinterpret_cast<Booster*>(handle);
+  const std::vector<double> imp = b->boosting->FeatureImportance(num_iteration, importance_type);
+  for (size_t i = 0; i < imp.size(); ++i) out_results[i] = imp[i];
+  API_END();
+}
+
+int LGBM_BoosterSaveModel(BoosterHandle handle, int start_iteration, int num_iteration, int /*feature_importance_type*/,
+                          const char* filename) {
+  API_BEGIN();
+  Booster* b = reinterpret_cast<Booster*>(handle);
+  const std::string model = b->boosting->SaveModelToString(start_iteration, num_iteration);
+  FILE* fh = std::fopen(filename, "wb");
+  if (fh == nullptr) Log::Fatal("Model file %s is not available for writes", filename);
+  const size_t n = std::fwrite(model.data(), 1, model.size(), fh);
+  std::fclose(fh);
+  if (n != model.size()) Log::Fatal("Could not write the model to %s", filename);
   API_END();
 }
 

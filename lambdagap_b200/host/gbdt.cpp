@@ -107,6 +107,8 @@ void GBDT::Bagging(int iter) {
   if (!bagging_ready_) {
     // ResetSampleConfig (bagging.hpp:139-201)
     bagging_ready_ = true;
+    bag_fraction_used_ = config_->bagging_fraction;
+    bag_freq_used_ = config_->bagging_freq;
     bag_data_cnt_ = static_cast<data_size_t>(config_->bagging_fraction * num_data_);
     if (bl == nullptr) {
       bag_data_indices_.resize(num_data_);
@@ -218,6 +220,33 @@ bool GBDT::TrainOneIter(const score_t* gradients, const score_t* hessians) {
   }
   ++iter_;
   return false;
+}
+
+std::vector<double> GBDT::FeatureImportance(int num_iteration, int importance_type) const {
+  int num_used_model = static_cast<int>(models_.size());
+  if (num_iteration > 0) num_used_model = std::min(num_iteration, num_used_model);
+  std::vector<double> imp(max_feature_idx_ + 1, 0.0);
+  if (importance_type != 0 && importance_type != 1) Log::Fatal("Unknown importance type: only support split=0 and gain=1");
+  for (int i = 0; i < num_used_model; ++i) {
+    for (int n = 0; n < models_[i]->num_leaves() - 1; ++n) {
+      if (models_[i]->split_gain(n) > 0) imp[models_[i]->split_feature(n)] += importance_type == 0 ? 1.0 : models_[i]->split_gain(n);
+    }
+  }
+  return imp;
+}
+
+void GBDT::ResetConfig(const Config* config) {
+  config_ = config;
+  shrinkage_rate_ = config->learning_rate;
+  if (tree_learner_ != nullptr) tree_learner_->ResetConfig(config);
+  // BaggingSampleStrategy::ResetSampleConfig (bagging.hpp:139-215): unchanged fraction / frequency keep the generators
+  // and the current bag; anything else starts over (generators re-seeded, next iteration re-bags)
+  const bool enabled = config->bagging_freq > 0 && config->bagging_fraction < 1.0;
+  if (enabled && bagging_ready_ && bag_fraction_used_ == config->bagging_fraction && bag_freq_used_ == config->bagging_freq) return;
+  const bool was_bagging = bagging_ready_;
+  bagging_ready_ = false;
+  bagging_rands_.clear();
+  if (was_bagging && !enabled) tree_learner_->SetBaggingData(nullptr, nullptr, 0);  // back to all rows
 }
 
 int64_t GBDT::GetNumPredictAt(int data_idx) const {

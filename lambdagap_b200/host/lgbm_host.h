@@ -239,6 +239,7 @@ class Tree {
   std::string ToString() const;                          // Tree::ToString (src/io/tree.cpp:339-395)
   const std::vector<double>& leaf_values() const { return leaf_value_; }
   int split_feature(int node) const { return split_feature_[node]; }
+  float split_gain(int node) const { return split_gain_[node]; }
 
  private:
   static double MaybeRoundToZero(double v) { return std::fabs(v) > kZeroThreshold ? v : 0.0; }
@@ -360,6 +361,9 @@ class B200TreeLearner : public TreeLearner {
   std::vector<int8_t> is_feature_used_;      // per inner feature
   int used_cnt_bytree_ = 0;
   bool need_reset_bytree_ = false;
+  gbl_learner_config last_config_{};
+  bool have_last_config_ = false;
+  double last_feature_fraction_ = 1.0;
   const Config* config_;
   gbl_comm* comm_;
   const Dataset* train_data_ = nullptr;
@@ -393,6 +397,11 @@ class GBDT {
   void PredictForMat(const void* data, int data_type, int32_t nrow, int32_t ncol, int is_row_major, bool raw_score,
                      double* out) const;
   int NumberOfTotalModel() const { return static_cast<int>(models_.size()); }
+  int MaxFeatureIdx() const { return max_feature_idx_; }
+  // GBDT::FeatureImportance (src/boosting/gbdt_model_text.cpp:627-661): 0 = split counts, 1 = total gains
+  std::vector<double> FeatureImportance(int num_iteration, int importance_type) const;
+  // GBDT::ResetConfig (src/boosting/gbdt.cpp:776-830) for the parameters this layer implements
+  void ResetConfig(const Config* config);
   int GetCurrentIteration() const { return iter_; }
   const std::vector<std::unique_ptr<Tree>>& models() const { return models_; }
   TreeLearner* tree_learner() { return tree_learner_.get(); }
@@ -405,6 +414,8 @@ class GBDT {
   std::vector<Random> bagging_rands_;     // one generator per block of 1024 rows (bagging.hpp:170-174); host path only
   std::vector<data_size_t> bag_data_indices_;
   bool bagging_ready_ = false;
+  double bag_fraction_used_ = 1.0;
+  int bag_freq_used_ = 0;
   data_size_t bag_data_cnt_ = 0;
   bool need_re_bagging_ = false;
   gbl_comm* comm_ = nullptr;

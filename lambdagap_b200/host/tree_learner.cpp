@@ -6,6 +6,7 @@
 // (src/treelearner/gradient_discretizer.cpp:16-41,116), ObjectiveFunction factory
 // (src/objective/objective_function.cpp:19-103).
 #include <algorithm>
+#include <cstring>
 #include <random>
 
 #include "lgbm_host.h"
@@ -97,6 +98,10 @@ void B200TreeLearner::Init(const Dataset* train_data, bool is_constant_hessian) 
   }
   gbl_learner_config c = MakeConfig();
   GblCheck(gbl_learner_create(train_data->device_handle(), &c, comm_, &handle_));
+  std::memset(&last_config_, 0, sizeof(last_config_));
+  last_config_ = c;
+  have_last_config_ = true;
+  last_feature_fraction_ = config_->feature_fraction;
   records_.resize(config_->num_leaves);
   quant_random_ready_ = false;
   if (config_->use_quantized_grad && config_->stochastic_rounding) InitQuantRandom();
@@ -143,11 +148,20 @@ void B200TreeLearner::ResetIsConstantHessian(bool is_constant_hessian) {
 }
 
 void B200TreeLearner::ResetConfig(const Config* config) {
+  const double old_fraction = config_ == config ? last_feature_fraction_ : config_->feature_fraction;
   config_ = config;
   gbl_learner_config c = MakeConfig();
-  GblCheck(gbl_learner_reset_config(handle_, &c));
+  // a learning-rate schedule resets the parameters before every iteration: only touch the device learner (which drops
+  // its captured tree) when a field it reads has changed
+  if (!have_last_config_ || std::memcmp(&c, &last_config_, sizeof(c)) != 0) {
+    GblCheck(gbl_learner_reset_config(handle_, &c));
+    last_config_ = c;
+    have_last_config_ = true;
+  }
   records_.resize(config_->num_leaves);
-  ColSamplerSetup(false);  // col_sampler_.SetConfig (serial_tree_learner.cpp:168)
+  if (col_seed_ != config_->feature_fraction_seed || old_fraction != config_->feature_fraction)
+    ColSamplerSetup(false);  // col_sampler_.SetConfig (serial_tree_learner.cpp:168)
+  last_feature_fraction_ = config_->feature_fraction;
 }
 
 void B200TreeLearner::SetBaggingData(const Dataset* /*subset*/, const data_size_t* used_indices, data_size_t num_data) {

@@ -126,6 +126,18 @@ class RefBooster:
                                                      hess.ctypes.data_as(ctypes.c_void_p), ctypes.byref(fin)))
         return fin.value
 
+    def reset_parameter(self, params):
+        """LGBM_BoosterResetParameter (src/c_api.cpp:2053)."""
+        _check(lib().LGBM_BoosterResetParameter(self.handle, ctypes.c_char_p(_params(params))))
+
+    def feature_importance(self, importance_type=0, num_iteration=-1):
+        n = ctypes.c_int(0)
+        _check(lib().LGBM_BoosterGetNumFeature(self.handle, ctypes.byref(n)))
+        out = np.zeros(n.value, dtype=np.float64)
+        _check(lib().LGBM_BoosterFeatureImportance(self.handle, ctypes.c_int(num_iteration), ctypes.c_int(importance_type),
+                                                   out.ctypes.data_as(ctypes.c_void_p)))
+        return out
+
     def add_valid(self, valid_set):
         """LGBM_BoosterAddValidData (src/c_api.cpp:2040)."""
         _check(lib().LGBM_BoosterAddValidData(self.handle, valid_set.handle))

@@ -142,3 +142,32 @@ def test_feature_fraction_by_tree(gpu, quant):
     # the derived seed (seed -> feature_fraction_seed, src/io/config.cpp:257-268) and a small fraction
     rb, ob = _train_both(X, y, "objective=binary num_leaves=15 seed=7 feature_fraction=0.2 min_data_in_leaf=20", 5)
     _compare_models(rb, ob, rtol=1e-5)
+
+
+def test_reset_parameter_and_model_queries(gpu, tmp_path):
+    """LGBM_BoosterResetParameter between iterations (a learning-rate schedule, then a different tree size and
+    regularisation), feature importances, leaf values and the saved model file, against the reference."""
+    X, y = H.make_binary(20000, 12, seed=29)
+    params = "objective=binary num_leaves=15 learning_rate=0.2 min_data_in_leaf=20 bagging_fraction=0.8 bagging_freq=1 bagging_seed=5"
+    common = "max_bin=255 verbose=-1 num_threads=4"
+    rds = R.RefDataset(X, y, params=common + " force_col_wise=true")
+    rb = R.RefBooster(rds, params + " device_type=cpu force_col_wise=true deterministic=true num_threads=4 verbose=-1")
+    ods = engine.Dataset(X, y, params=common)
+    ob = engine.Booster(ods, params + " device_type=cuda num_threads=4 verbose=-1")
+    schedule = ["learning_rate=0.2", "learning_rate=0.1", "learning_rate=0.05", "learning_rate=0.05 num_leaves=31 lambda_l2=2.0",
+                "learning_rate=0.05 num_leaves=31 lambda_l2=2.0 bagging_fraction=0.7", "min_data_in_leaf=100"]  # (0.5 would switch the reference CPU learner to its subset mode, which aborts on this schedule)
+    for step in schedule:
+        rb.reset_parameter(step)
+        ob.reset_parameter(step)
+        rb.update()
+        ob.update()
+    _compare_models(rb, ob, rtol=1e-5)
+    np.testing.assert_array_equal(ob.feature_importance(0), rb.feature_importance(0))
+    np.testing.assert_allclose(ob.feature_importance(1), rb.feature_importance(1), rtol=1e-5)
+    trees = R.parse_model_trees(ob.model_to_string())
+    assert ob.leaf_value(3, 2) == trees[3]["leaf_value"][2]
+    path = str(tmp_path / "model.txt")
+    ob.save_model(path)
+    assert open(path).read() == ob.model_to_string()
+    with pytest.raises(engine.LightGBMError, match="Cannot change"):
+        ob.reset_parameter("metric=auc")
