@@ -177,6 +177,12 @@ GBL_API int gbl_learner_set_bagging_data(gbl_learner* learner, const int32_t* us
  * row trains on every row.  Same restrictions as gbl_learner_set_bagging_data. */
 GBL_API int gbl_learner_bagging_dev(gbl_learner* learner, int32_t bagging_seed, double bagging_fraction, int32_t reset,
                                     int32_t* out_bag_count);
+/* BalancedBaggingHelper (src/boosting/bagging.hpp:245-270): the same draw, with pos_bagging_fraction for rows whose label
+ * is positive and neg_bagging_fraction for the others.  label_host[num_data] is copied to the device when given (first
+ * call, or when the labels changed); NULL reuses the previous copy. */
+GBL_API int gbl_learner_bagging_balanced_dev(gbl_learner* learner, int32_t bagging_seed, double pos_bagging_fraction,
+                                             double neg_bagging_fraction, const float* label_host, int32_t reset,
+                                             int32_t* out_bag_count);
 /* GradientDiscretizer's host-generated uniform [0,1) arrays for stochastic rounding
  * (src/treelearner/gradient_discretizer.cpp:16-41) and the per-iteration start offset (:116).  */
 GBL_API int gbl_learner_set_quant_random(gbl_learner* learner, const double* grad_random_host,

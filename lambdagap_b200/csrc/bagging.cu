@@ -23,8 +23,12 @@ __global__ void __launch_bounds__(128) bag_seed_kernel(unsigned* __restrict__ st
   if (b < nblk) state[b] = static_cast<unsigned>(seed + b);  // bagging_rands_.emplace_back(bagging_seed + i)
 }
 
+// label == nullptr: BaggingHelper (every row against `fraction`); otherwise BalancedBaggingHelper (bagging.hpp:245-270):
+// rows with label > 0 against pos_fraction, the others against neg_fraction -- one draw per row either way
 __global__ void __launch_bounds__(128) bag_draw_kernel(unsigned* __restrict__ state, int nblk, int n, double fraction,
-                                                       unsigned* __restrict__ bits, int* __restrict__ blk_cnt) {
+                                                       const float* __restrict__ label, double pos_fraction,
+                                                       double neg_fraction, unsigned* __restrict__ bits,
+                                                       int* __restrict__ blk_cnt) {
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= nblk) return;
   unsigned x = state[b];
@@ -37,7 +41,8 @@ __global__ void __launch_bounds__(128) bag_draw_kernel(unsigned* __restrict__ st
       if (row < n) {
         x = 214013u * x + 2531011u;  // Random::RandInt16
         const float f = static_cast<float>(static_cast<int>((x >> 16) & 0x7FFF)) / 32768.0f;  // NextFloat
-        if (static_cast<double>(f) < fraction) word |= 1u << k;  // bagging.hpp:233
+        const double limit = label == nullptr ? fraction : (label[row] > 0 ? pos_fraction : neg_fraction);
+        if (static_cast<double>(f) < limit) word |= 1u << k;  // bagging.hpp:233 / :255-262
       }
     }
     bits[static_cast<size_t>(b) * (kBagBlock / 32) + w] = word;
@@ -120,9 +125,11 @@ void launch_bag_seed(unsigned* state, int nblk, int seed, cudaStream_t s) {
   GBL_LAUNCH(bag_seed_kernel, (nblk + 127) / 128, 128, 0, s, state, nblk, seed);
 }
 
-void launch_bag_draw(unsigned* state, int nblk, int n, double fraction, unsigned* bits, int* blk_cnt, int* blk_off,
-                     int* counts, int* bag, int* oob, cudaStream_t s) {
-  GBL_LAUNCH(bag_draw_kernel, (nblk + 127) / 128, 128, 0, s, state, nblk, n, fraction, bits, blk_cnt);
+void launch_bag_draw(unsigned* state, int nblk, int n, double fraction, const float* label, double pos_fraction,
+                     double neg_fraction, unsigned* bits, int* blk_cnt, int* blk_off, int* counts, int* bag, int* oob,
+                     cudaStream_t s) {
+  GBL_LAUNCH(bag_draw_kernel, (nblk + 127) / 128, 128, 0, s, state, nblk, n, fraction, label, pos_fraction, neg_fraction, bits,
+             blk_cnt);
   GBL_LAUNCH(bag_scan_kernel, 1, 1024, 0, s, blk_cnt, nblk, n, blk_off, counts);
   GBL_LAUNCH(bag_write_kernel, (nblk + 7) / 8, 256, 0, s, bits, blk_off, nblk, n, bag, oob);
 }

@@ -76,6 +76,7 @@ struct Learner {
   int* bag_counts_dev = nullptr;
   int* bag_counts_pinned = nullptr;
   int bag_seed = 0;
+  float* bag_label = nullptr;  // balanced bagging: the labels that pick a row's fraction
   float* grad_stage = nullptr;  // train_host staging
   float* hess_stage = nullptr;
   long long* tap_hist = nullptr;
@@ -400,6 +401,7 @@ static void learner_free(Learner* L) {
   cudaFree(L->bag_blk_cnt);
   cudaFree(L->bag_blk_off);
   cudaFree(L->bag_counts_dev);
+  cudaFree(L->bag_label);
   if (L->bag_counts_pinned) cudaFreeHost(L->bag_counts_pinned);
   cudaFree(L->grad_stage);
   cudaFree(L->hess_stage);
@@ -940,17 +942,25 @@ int gbl_learner_set_bagging_data(gbl_learner* learner, const int32_t* used_indic
   GBL_API_END();
 }
 
-int gbl_learner_bagging_dev(gbl_learner* learner, int32_t bagging_seed, double bagging_fraction, int32_t reset,
-                            int32_t* out_bag_count) {
-  GBL_API_BEGIN();
-  Learner* L = LEARNER(learner);
-  if (L == nullptr) fatal("gbl_learner_bagging_dev: null learner");
-  if (!(bagging_fraction > 0.0 && bagging_fraction <= 1.0)) fatal("gbl_learner_bagging_dev: bagging_fraction must be in (0, 1]");
+static void bagging_dev(Learner* L, int32_t bagging_seed, double fraction, bool balanced, double pos_fraction,
+                        double neg_fraction, const float* label_host, int32_t reset, int32_t* out_bag_count) {
+  auto in_unit = [](double f) { return f > 0.0 && f <= 1.0; };
+  if (!balanced && !in_unit(fraction)) fatal("gbl_learner_bagging_dev: bagging_fraction must be in (0, 1]");
+  if (balanced && (!in_unit(pos_fraction) || !in_unit(neg_fraction)))
+    fatal("gbl_learner_bagging_balanced_dev: pos_bagging_fraction / neg_bagging_fraction must be in (0, 1]");
   if (L->comm != nullptr && L->comm->num_ranks > 1) fatal("learner: bagging with the data-parallel learner is not supported");
   if (L->cfg.use_quantized_grad) fatal("learner: bagging with use_quantized_grad is not supported");
   DeviceGuard guard(L->ds->device);
   const int n = static_cast<int>(L->ds->num_data);
   const int nblk = (n + 1023) / 1024;
+  if (balanced) {
+    if (label_host != nullptr) {
+      if (L->bag_label == nullptr) GBL_CUDA(cudaMalloc(&L->bag_label, sizeof(float) * n));
+      GBL_CUDA(cudaMemcpyAsync(L->bag_label, label_host, sizeof(float) * n, cudaMemcpyHostToDevice, L->stream));
+    } else if (L->bag_label == nullptr) {
+      fatal("gbl_learner_bagging_balanced_dev: the first call needs the labels");
+    }
+  }
   if (L->bag_state == nullptr) {
     GBL_CUDA(cudaMalloc(&L->bag_state, sizeof(unsigned) * nblk));
     GBL_CUDA(cudaMalloc(&L->bag_bits, sizeof(unsigned) * nblk * 32));
@@ -972,13 +982,31 @@ int gbl_learner_bagging_dev(gbl_learner* learner, int32_t bagging_seed, double b
     launch_bag_seed(L->bag_state, nblk, bagging_seed, L->stream);
     L->bag_seed = bagging_seed;
   }
-  launch_bag_draw(L->bag_state, nblk, n, bagging_fraction, L->bag_bits, L->bag_blk_cnt, L->bag_blk_off, L->bag_counts_dev,
-                  L->bag_indices, L->oob_indices, L->stream);
+  launch_bag_draw(L->bag_state, nblk, n, fraction, balanced ? L->bag_label : nullptr, pos_fraction, neg_fraction, L->bag_bits,
+                  L->bag_blk_cnt, L->bag_blk_off, L->bag_counts_dev, L->bag_indices, L->oob_indices, L->stream);
   GBL_CUDA(cudaMemcpyAsync(L->bag_counts_pinned, L->bag_counts_dev, sizeof(int) * 2, cudaMemcpyDeviceToHost, L->stream));
   GBL_CUDA(cudaStreamSynchronize(L->stream));
   L->bag_count = L->bag_counts_pinned[0];
   L->oob_count = L->bag_counts_pinned[1];
   if (out_bag_count != nullptr) *out_bag_count = L->bag_count;
+}
+
+int gbl_learner_bagging_dev(gbl_learner* learner, int32_t bagging_seed, double bagging_fraction, int32_t reset,
+                            int32_t* out_bag_count) {
+  GBL_API_BEGIN();
+  Learner* L = LEARNER(learner);
+  if (L == nullptr) fatal("gbl_learner_bagging_dev: null learner");
+  bagging_dev(L, bagging_seed, bagging_fraction, false, 1.0, 1.0, nullptr, reset, out_bag_count);
+  GBL_API_END();
+}
+
+int gbl_learner_bagging_balanced_dev(gbl_learner* learner, int32_t bagging_seed, double pos_bagging_fraction,
+                                     double neg_bagging_fraction, const float* label_host, int32_t reset,
+                                     int32_t* out_bag_count) {
+  GBL_API_BEGIN();
+  Learner* L = LEARNER(learner);
+  if (L == nullptr) fatal("gbl_learner_bagging_balanced_dev: null learner");
+  bagging_dev(L, bagging_seed, 1.0, true, pos_bagging_fraction, neg_bagging_fraction, label_host, reset, out_bag_count);
   GBL_API_END();
 }
 

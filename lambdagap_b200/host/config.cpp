@@ -278,14 +278,13 @@ void Config::Set(const std::string& parameters) {
   if (extra_trees) Log::Fatal("extra_trees is not supported by the B200 learner");
   if (feature_fraction_bynode < 1.0) Log::Fatal("feature_fraction_bynode < 1 is not supported by the B200 learner");
   if (feature_fraction <= 0.0 || feature_fraction > 1.0) Log::Fatal("feature_fraction should be in (0.0, 1.0]");
-  if (bagging_freq > 0 && bagging_fraction < 1.0) {
+  if (bagging_freq > 0 && (bagging_fraction < 1.0 || pos_bagging_fraction < 1.0 || neg_bagging_fraction < 1.0)) {
     if (use_quantized_grad)
       Log::Fatal("bagging with use_quantized_grad is not supported by the B200 learner (the reference's bagged quantized "
                  "LeafSplits::Init indexes the gradients by position, leaf_splits.hpp:185)");
     if (tree_learner != "serial") Log::Fatal("bagging with tree_learner=%s is not supported by the B200 learner", tree_learner.c_str());
     if (bagging_by_query) Log::Fatal("bagging_by_query is not supported by the B200 learner");
   }
-  if (pos_bagging_fraction < 1.0 || neg_bagging_fraction < 1.0) Log::Fatal("balanced bagging is not supported by the B200 learner");
   if (max_bin > 255) Log::Fatal("max_bin=%d: the B200 learner stores one byte per cell (max_bin <= 255)", max_bin);
   if (num_leaves < 2) Log::Fatal("num_leaves must be at least 2");
   for (const char* k : {"monotone_constraints", "interaction_constraints", "forcedsplits_filename", "categorical_feature",

@@ -99,17 +99,40 @@ void GBDT::Init(const Config* config, const Dataset* train_data, ObjectiveFuncti
 // 1024 rows (seeded bagging_seed + block, state carried from iteration to iteration) and is in the bag when the draw
 // is below bagging_fraction; the in-bag rows are handed to the learner in ascending order.  Block-wise generators
 // make the result independent of the number of threads, so this sequential version draws the reference's bag.
+// bagging.hpp:146-147: plain bagging, or balanced bagging when a positive / negative fraction is set and the objective
+// counts positive rows (binary only: ObjectiveFunction::NumPositiveData is 0 elsewhere)
+bool GBDT::BaggingEnabled(const Config* config, bool* balanced) const {
+  data_size_t num_pos = 0;
+  if (objective_function_ != nullptr && std::string(objective_function_->GetName()) == "binary") {
+    for (label_t l : train_data_->metadata().label) num_pos += l > 0 ? 1 : 0;
+  }
+  *balanced = (config->pos_bagging_fraction < 1.0 || config->neg_bagging_fraction < 1.0) && num_pos > 0;
+  return (config->bagging_fraction < 1.0 || *balanced) && config->bagging_freq > 0;
+}
+
 void GBDT::Bagging(int iter) {
-  const bool enabled = config_->bagging_freq > 0 && config_->bagging_fraction < 1.0;
-  if (!enabled) return;
+  if (!bagging_ready_) {
+    bool balanced = false;
+    if (!BaggingEnabled(config_, &balanced)) return;
+    balanced_bagging_ = balanced;
+  }
   B200TreeLearner* bl = dynamic_cast<B200TreeLearner*>(tree_learner_.get());
   constexpr int kBlock = 1024;  // bagging_rand_block_
   if (!bagging_ready_) {
     // ResetSampleConfig (bagging.hpp:139-201)
     bagging_ready_ = true;
     bag_fraction_used_ = config_->bagging_fraction;
+    bag_pos_used_ = config_->pos_bagging_fraction;
+    bag_neg_used_ = config_->neg_bagging_fraction;
     bag_freq_used_ = config_->bagging_freq;
-    bag_data_cnt_ = static_cast<data_size_t>(config_->bagging_fraction * num_data_);
+    if (balanced_bagging_) {
+      data_size_t num_pos = 0;
+      for (label_t l : train_data_->metadata().label) num_pos += l > 0 ? 1 : 0;
+      bag_data_cnt_ = static_cast<data_size_t>(num_pos * config_->pos_bagging_fraction) +
+                      static_cast<data_size_t>((num_data_ - num_pos) * config_->neg_bagging_fraction);
+    } else {
+      bag_data_cnt_ = static_cast<data_size_t>(config_->bagging_fraction * num_data_);
+    }
     if (bl == nullptr) {
       bag_data_indices_.resize(num_data_);
       for (int i = 0; i < (num_data_ + kBlock - 1) / kBlock; ++i) bagging_rands_.emplace_back(config_->bagging_seed + i);
@@ -122,14 +145,22 @@ void GBDT::Bagging(int iter) {
   if (bl != nullptr) {
     // the same draw on the device: one thread per block generator, compaction by a prefix scan; nothing but the
     // bag size crosses PCIe
-    bag_data_cnt_ = bl->BaggingOnDevice(config_->bagging_seed, config_->bagging_fraction, first);
+    if (balanced_bagging_) {
+      bag_data_cnt_ = bl->BalancedBaggingOnDevice(config_->bagging_seed, config_->pos_bagging_fraction, config_->neg_bagging_fraction,
+                                                  first ? train_data_->metadata().label.data() : nullptr, first);
+    } else {
+      bag_data_cnt_ = bl->BaggingOnDevice(config_->bagging_seed, config_->bagging_fraction, first);
+    }
     Log::Debug("Re-bagging, using %d data to train", bag_data_cnt_);
     return;
   }
   data_size_t cnt = 0;
+  const std::vector<label_t>& label = train_data_->metadata().label;
   for (data_size_t i = 0; i < num_data_; ++i) {
-    // bagging.hpp:233: `NextFloat() < config_->bagging_fraction` (float promoted to double)
-    if (static_cast<double>(bagging_rands_[i / kBlock].NextFloat()) < config_->bagging_fraction) bag_data_indices_[cnt++] = i;
+    // bagging.hpp:233 / :255-262: `NextFloat() < fraction` (float promoted to double)
+    const double limit = !balanced_bagging_ ? config_->bagging_fraction
+                                            : (label[i] > 0 ? config_->pos_bagging_fraction : config_->neg_bagging_fraction);
+    if (static_cast<double>(bagging_rands_[i / kBlock].NextFloat()) < limit) bag_data_indices_[cnt++] = i;
   }
   bag_data_cnt_ = cnt;
   Log::Debug("Re-bagging, using %d data to train", bag_data_cnt_);
@@ -241,8 +272,11 @@ void GBDT::ResetConfig(const Config* config) {
   if (tree_learner_ != nullptr) tree_learner_->ResetConfig(config);
   // BaggingSampleStrategy::ResetSampleConfig (bagging.hpp:139-215): unchanged fraction / frequency keep the generators
   // and the current bag; anything else starts over (generators re-seeded, next iteration re-bags)
-  const bool enabled = config->bagging_freq > 0 && config->bagging_fraction < 1.0;
-  if (enabled && bagging_ready_ && bag_fraction_used_ == config->bagging_fraction && bag_freq_used_ == config->bagging_freq) return;
+  bool balanced = false;
+  const bool enabled = BaggingEnabled(config, &balanced);
+  if (enabled && bagging_ready_ && bag_fraction_used_ == config->bagging_fraction && bag_freq_used_ == config->bagging_freq &&
+      bag_pos_used_ == config->pos_bagging_fraction && bag_neg_used_ == config->neg_bagging_fraction)
+    return;
   const bool was_bagging = bagging_ready_;
   bagging_ready_ = false;
   bagging_rands_.clear();

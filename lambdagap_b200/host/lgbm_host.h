@@ -341,6 +341,8 @@ class B200TreeLearner : public TreeLearner {
   gbl_learner* handle() const { return handle_; }
   // BaggingSampleStrategy::Bagging drawn on the device (the reference's bag, bit for bit); returns the bag size
   data_size_t BaggingOnDevice(int bagging_seed, double bagging_fraction, bool reset);
+  // BalancedBaggingHelper on the device; `label` is uploaded when not null
+  data_size_t BalancedBaggingOnDevice(int bagging_seed, double pos_fraction, double neg_fraction, const label_t* label, bool reset);
   // device-resident pipeline used by GBDT: enqueue the tree, update the scores from the leaf outputs that are
   // still on the device, and only then wait for the split records
   void TrainAsync(const score_t* gradients, const score_t* hessians);
@@ -414,7 +416,9 @@ class GBDT {
   std::vector<Random> bagging_rands_;     // one generator per block of 1024 rows (bagging.hpp:170-174); host path only
   std::vector<data_size_t> bag_data_indices_;
   bool bagging_ready_ = false;
-  double bag_fraction_used_ = 1.0;
+  double bag_fraction_used_ = 1.0, bag_pos_used_ = 1.0, bag_neg_used_ = 1.0;
+  bool balanced_bagging_ = false;
+  bool BaggingEnabled(const Config* config, bool* balanced) const;
   int bag_freq_used_ = 0;
   data_size_t bag_data_cnt_ = 0;
   bool need_re_bagging_ = false;

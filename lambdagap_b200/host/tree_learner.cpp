@@ -174,6 +174,13 @@ data_size_t B200TreeLearner::BaggingOnDevice(int bagging_seed, double bagging_fr
   return cnt;
 }
 
+data_size_t B200TreeLearner::BalancedBaggingOnDevice(int bagging_seed, double pos_fraction, double neg_fraction,
+                                                     const label_t* label, bool reset) {
+  int32_t cnt = 0;
+  GblCheck(gbl_learner_bagging_balanced_dev(handle_, bagging_seed, pos_fraction, neg_fraction, label, reset ? 1 : 0, &cnt));
+  return cnt;
+}
+
 Tree* B200TreeLearner::Train(const score_t* gradients, const score_t* hessians, bool /*is_first_tree*/) {
   TrainAsync(gradients, hessians);
   return FinishTrain();

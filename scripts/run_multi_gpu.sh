@@ -1,3 +1,4 @@
+# Usage: bash scripts/run_multi_gpu.sh N   (N = GPUs of one node): N-GPU trees == 1-GPU trees, then the bench at N GPUs on both workloads
 N=$1
 timeout 200 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 scripts/check_multi_gpu.py > gpurun_out/check_mg$N.log 2>&1
 echo "check rc=$?"; tail -3 gpurun_out/check_mg$N.log

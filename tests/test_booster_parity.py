@@ -171,3 +171,14 @@ def test_reset_parameter_and_model_queries(gpu, tmp_path):
     assert open(path).read() == ob.model_to_string()
     with pytest.raises(engine.LightGBMError, match="Cannot change"):
         ob.reset_parameter("metric=auc")
+
+
+def test_balanced_bagging(gpu):
+    """pos_bagging_fraction / neg_bagging_fraction (BalancedBaggingHelper, src/boosting/bagging.hpp:245-270): the label
+    picks the fraction a row's draw is compared with; drawn on the device, trees equal the reference's."""
+    X, y = H.make_binary(40000, 14, seed=31, zero_frac=0.1)
+    params = ("objective=binary num_leaves=31 learning_rate=0.1 min_data_in_leaf=20 pos_bagging_fraction=0.6 "
+              "neg_bagging_fraction=0.9 bagging_freq=1 bagging_seed=9")
+    rb, ob = _train_both(X, y, params, 8)
+    _compare_models(rb, ob, rtol=1e-5, exact_counts=True)
+    np.testing.assert_allclose(ob.train_scores(raw=True), rb.train_scores_raw(), rtol=1e-5, atol=1e-8)
