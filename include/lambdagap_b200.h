@@ -180,6 +180,11 @@ GBL_API int gbl_learner_bagging_dev(gbl_learner* learner, int32_t bagging_seed, 
 /* BalancedBaggingHelper (src/boosting/bagging.hpp:245-270): the same draw, with pos_bagging_fraction for rows whose label
  * is positive and neg_bagging_fraction for the others.  label_host[num_data] is copied to the device when given (first
  * call, or when the labels changed); NULL reuses the previous copy. */
+/* bagging_by_query (src/boosting/bagging.hpp:54-99): the draw runs over queries (generators per block of 1024 QUERIES) and
+ * a row is in the bag when its query is.  query_boundaries_host[num_queries + 1] is copied when given; NULL reuses it. */
+GBL_API int gbl_learner_bagging_by_query_dev(gbl_learner* learner, int32_t bagging_seed, double bagging_fraction,
+                                             const int32_t* query_boundaries_host, int32_t num_queries, int32_t reset,
+                                             int32_t* out_bag_count);
 GBL_API int gbl_learner_bagging_balanced_dev(gbl_learner* learner, int32_t bagging_seed, double pos_bagging_fraction,
                                              double neg_bagging_fraction, const float* label_host, int32_t reset,
                                              int32_t* out_bag_count);

@@ -81,7 +81,7 @@ EXPORTED_SYMBOLS = [
     "gbl_dataset_get_feature_bins", "gbl_dataset_get_feature_bins_rowmajor",
     "gbl_comm_get_unique_id", "gbl_comm_create", "gbl_comm_free", "gbl_comm_allreduce_host_f64", "gbl_comm_info",
     "gbl_learner_create", "gbl_learner_free", "gbl_learner_reset_config", "gbl_learner_set_feature_mask",
-    "gbl_learner_set_bagging_data", "gbl_learner_bagging_dev", "gbl_learner_bagging_balanced_dev", "gbl_learner_set_quant_random", "gbl_learner_set_quant_random_start",
+    "gbl_learner_set_bagging_data", "gbl_learner_bagging_dev", "gbl_learner_bagging_balanced_dev", "gbl_learner_bagging_by_query_dev", "gbl_learner_set_quant_random", "gbl_learner_set_quant_random_start",
     "gbl_learner_train", "gbl_learner_train_host", "gbl_learner_train_async", "gbl_learner_train_finish",
     "gbl_learner_add_prediction_to_score", "gbl_learner_add_prediction_to_score_dev",
     "gbl_learner_add_prediction_out_of_bag_dev", "gbl_learner_add_prediction_to_dataset_dev", "gbl_learner_get_leaf_values", "gbl_learner_get_leaf_assignment", "gbl_learner_get_leaf_indices", "gbl_learner_get_histogram",

@@ -121,6 +121,40 @@ __global__ void __launch_bounds__(256) bag_write_kernel(const unsigned* __restri
   }
 }
 
+// bagging_by_query (bagging.hpp:54-99): the draw runs over QUERIES (qbits: 1 bit per query); a row is in the bag when its
+// query is.  One warp per block of 1024 rows builds the row-level bits and the block's count from row_query[].
+__global__ void __launch_bounds__(256) bag_rows_from_queries_kernel(const unsigned* __restrict__ qbits,
+                                                                    const int* __restrict__ row_query, int nblk, int n,
+                                                                    unsigned* __restrict__ bits, int* __restrict__ blk_cnt) {
+  const int lane = threadIdx.x & 31;
+  const int b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (b >= nblk) return;
+  const int begin = b * kBagBlock + lane * 32;
+  unsigned word = 0u;
+  for (int k = 0; k < 32; ++k) {
+    const int row = begin + k;
+    if (row < n) {
+      const int q = row_query[row];
+      word |= ((qbits[q >> 5] >> (q & 31)) & 1u) << k;
+    }
+  }
+  bits[static_cast<size_t>(b) * (kBagBlock / 32) + lane] = word;
+  int cnt = __popc(word);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) cnt += __shfl_down_sync(0xffffffffu, cnt, o);
+  if (lane == 0) blk_cnt[b] = cnt;
+}
+
+void launch_bag_draw_by_query(unsigned* state, int nblk_q, int nq, double fraction, unsigned* qbits, int* qblk_cnt,
+                              const int* row_query, int nblk, int n, unsigned* bits, int* blk_cnt, int* blk_off, int* counts,
+                              int* bag, int* oob, cudaStream_t s) {
+  GBL_LAUNCH(bag_draw_kernel, (nblk_q + 127) / 128, 128, 0, s, state, nblk_q, nq, fraction, static_cast<const float*>(nullptr),
+             1.0, 1.0, qbits, qblk_cnt);
+  GBL_LAUNCH(bag_rows_from_queries_kernel, (nblk + 7) / 8, 256, 0, s, qbits, row_query, nblk, n, bits, blk_cnt);
+  GBL_LAUNCH(bag_scan_kernel, 1, 1024, 0, s, blk_cnt, nblk, n, blk_off, counts);
+  GBL_LAUNCH(bag_write_kernel, (nblk + 7) / 8, 256, 0, s, bits, blk_off, nblk, n, bag, oob);
+}
+
 void launch_bag_seed(unsigned* state, int nblk, int seed, cudaStream_t s) {
   GBL_LAUNCH(bag_seed_kernel, (nblk + 127) / 128, 128, 0, s, state, nblk, seed);
 }

@@ -109,6 +109,9 @@ void launch_xchg_reduce(const LearnerDev& d, int is_root, cudaStream_t s);
 void launch_xchg_max(const LearnerDev& d, cudaStream_t s);
 // bagging.cu
 void launch_bag_seed(unsigned* state, int nblk, int seed, cudaStream_t s);
+void launch_bag_draw_by_query(unsigned* state, int nblk_q, int nq, double fraction, unsigned* qbits, int* qblk_cnt,
+                              const int* row_query, int nblk, int n, unsigned* bits, int* blk_cnt, int* blk_off, int* counts,
+                              int* bag, int* oob, cudaStream_t s);
 void launch_bag_draw(unsigned* state, int nblk, int n, double fraction, const float* label, double pos_fraction,
                      double neg_fraction, unsigned* bits, int* blk_cnt, int* blk_off, int* counts, int* bag, int* oob,
                      cudaStream_t s);

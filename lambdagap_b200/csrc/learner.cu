@@ -77,6 +77,10 @@ struct Learner {
   int* bag_counts_pinned = nullptr;
   int bag_seed = 0;
   float* bag_label = nullptr;  // balanced bagging: the labels that pick a row's fraction
+  int* bag_row_query = nullptr;     // bagging by query: query of every row
+  unsigned* bag_qbits = nullptr;    // 1 bit per query
+  int* bag_qblk_cnt = nullptr;
+  int bag_num_queries = 0;
   float* grad_stage = nullptr;  // train_host staging
   float* hess_stage = nullptr;
   long long* tap_hist = nullptr;
@@ -402,6 +406,9 @@ static void learner_free(Learner* L) {
   cudaFree(L->bag_blk_off);
   cudaFree(L->bag_counts_dev);
   cudaFree(L->bag_label);
+  cudaFree(L->bag_row_query);
+  cudaFree(L->bag_qbits);
+  cudaFree(L->bag_qblk_cnt);
   if (L->bag_counts_pinned) cudaFreeHost(L->bag_counts_pinned);
   cudaFree(L->grad_stage);
   cudaFree(L->hess_stage);
@@ -943,7 +950,8 @@ int gbl_learner_set_bagging_data(gbl_learner* learner, const int32_t* used_indic
 }
 
 static void bagging_dev(Learner* L, int32_t bagging_seed, double fraction, bool balanced, double pos_fraction,
-                        double neg_fraction, const float* label_host, int32_t reset, int32_t* out_bag_count) {
+                        double neg_fraction, const float* label_host, int32_t reset, int32_t* out_bag_count,
+                        const int32_t* query_boundaries_host = nullptr, int32_t num_queries = 0, bool by_query = false) {
   auto in_unit = [](double f) { return f > 0.0 && f <= 1.0; };
   if (!balanced && !in_unit(fraction)) fatal("gbl_learner_bagging_dev: bagging_fraction must be in (0, 1]");
   if (balanced && (!in_unit(pos_fraction) || !in_unit(neg_fraction)))
@@ -959,6 +967,29 @@ static void bagging_dev(Learner* L, int32_t bagging_seed, double fraction, bool 
       GBL_CUDA(cudaMemcpyAsync(L->bag_label, label_host, sizeof(float) * n, cudaMemcpyHostToDevice, L->stream));
     } else if (L->bag_label == nullptr) {
       fatal("gbl_learner_bagging_balanced_dev: the first call needs the labels");
+    }
+  }
+  if (by_query) {
+    if (query_boundaries_host != nullptr) {
+      if (num_queries <= 0 || query_boundaries_host[0] != 0 || query_boundaries_host[num_queries] != n)
+        fatal("gbl_learner_bagging_by_query_dev: query boundaries must cover rows 0..num_data");
+      std::vector<int> row_query(n);
+      for (int q = 0; q < num_queries; ++q) {
+        if (query_boundaries_host[q + 1] < query_boundaries_host[q]) fatal("gbl_learner_bagging_by_query_dev: boundaries must not decrease");
+        for (int r = query_boundaries_host[q]; r < query_boundaries_host[q + 1]; ++r) row_query[r] = q;
+      }
+      cudaFree(L->bag_row_query);
+      cudaFree(L->bag_qbits);
+      cudaFree(L->bag_qblk_cnt);
+      L->bag_row_query = nullptr;
+      const int nblk_q = (num_queries + 1023) / 1024;
+      GBL_CUDA(cudaMalloc(&L->bag_row_query, sizeof(int) * n));
+      GBL_CUDA(cudaMalloc(&L->bag_qbits, sizeof(unsigned) * nblk_q * 32));
+      GBL_CUDA(cudaMalloc(&L->bag_qblk_cnt, sizeof(int) * nblk_q));
+      GBL_CUDA(cudaMemcpy(L->bag_row_query, row_query.data(), sizeof(int) * n, cudaMemcpyHostToDevice));
+      L->bag_num_queries = num_queries;
+    } else if (L->bag_row_query == nullptr) {
+      fatal("gbl_learner_bagging_by_query_dev: the first call needs the query boundaries");
     }
   }
   if (L->bag_state == nullptr) {
@@ -982,8 +1013,15 @@ static void bagging_dev(Learner* L, int32_t bagging_seed, double fraction, bool 
     launch_bag_seed(L->bag_state, nblk, bagging_seed, L->stream);
     L->bag_seed = bagging_seed;
   }
-  launch_bag_draw(L->bag_state, nblk, n, fraction, balanced ? L->bag_label : nullptr, pos_fraction, neg_fraction, L->bag_bits,
-                  L->bag_blk_cnt, L->bag_blk_off, L->bag_counts_dev, L->bag_indices, L->oob_indices, L->stream);
+  if (by_query) {
+    // the generators are indexed by QUERY block (bagging.hpp:36-66 runs BaggingHelper over num_queries_ items)
+    launch_bag_draw_by_query(L->bag_state, (L->bag_num_queries + 1023) / 1024, L->bag_num_queries, fraction, L->bag_qbits,
+                             L->bag_qblk_cnt, L->bag_row_query, nblk, n, L->bag_bits, L->bag_blk_cnt, L->bag_blk_off,
+                             L->bag_counts_dev, L->bag_indices, L->oob_indices, L->stream);
+  } else {
+    launch_bag_draw(L->bag_state, nblk, n, fraction, balanced ? L->bag_label : nullptr, pos_fraction, neg_fraction, L->bag_bits,
+                    L->bag_blk_cnt, L->bag_blk_off, L->bag_counts_dev, L->bag_indices, L->oob_indices, L->stream);
+  }
   GBL_CUDA(cudaMemcpyAsync(L->bag_counts_pinned, L->bag_counts_dev, sizeof(int) * 2, cudaMemcpyDeviceToHost, L->stream));
   GBL_CUDA(cudaStreamSynchronize(L->stream));
   L->bag_count = L->bag_counts_pinned[0];
@@ -1007,6 +1045,17 @@ int gbl_learner_bagging_balanced_dev(gbl_learner* learner, int32_t bagging_seed,
   Learner* L = LEARNER(learner);
   if (L == nullptr) fatal("gbl_learner_bagging_balanced_dev: null learner");
   bagging_dev(L, bagging_seed, 1.0, true, pos_bagging_fraction, neg_bagging_fraction, label_host, reset, out_bag_count);
+  GBL_API_END();
+}
+
+int gbl_learner_bagging_by_query_dev(gbl_learner* learner, int32_t bagging_seed, double bagging_fraction,
+                                     const int32_t* query_boundaries_host, int32_t num_queries, int32_t reset,
+                                     int32_t* out_bag_count) {
+  GBL_API_BEGIN();
+  Learner* L = LEARNER(learner);
+  if (L == nullptr) fatal("gbl_learner_bagging_by_query_dev: null learner");
+  bagging_dev(L, bagging_seed, bagging_fraction, false, 1.0, 1.0, nullptr, reset, out_bag_count, query_boundaries_host,
+              num_queries, true);
   GBL_API_END();
 }
 

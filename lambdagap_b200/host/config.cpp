@@ -283,7 +283,6 @@ void Config::Set(const std::string& parameters) {
       Log::Fatal("bagging with use_quantized_grad is not supported by the B200 learner (the reference's bagged quantized "
                  "LeafSplits::Init indexes the gradients by position, leaf_splits.hpp:185)");
     if (tree_learner != "serial") Log::Fatal("bagging with tree_learner=%s is not supported by the B200 learner", tree_learner.c_str());
-    if (bagging_by_query) Log::Fatal("bagging_by_query is not supported by the B200 learner");
   }
   if (max_bin > 255) Log::Fatal("max_bin=%d: the B200 learner stores one byte per cell (max_bin <= 255)", max_bin);
   if (num_leaves < 2) Log::Fatal("num_leaves must be at least 2");

@@ -145,7 +145,14 @@ void GBDT::Bagging(int iter) {
   if (bl != nullptr) {
     // the same draw on the device: one thread per block generator, compaction by a prefix scan; nothing but the
     // bag size crosses PCIe
-    if (balanced_bagging_) {
+    if (config_->bagging_by_query) {
+      // bagging.hpp:54-99: queries are drawn, their documents form the bag.  The reference then computes gradients for
+      // the sampled queries only (gbdt.cpp:229-232); computing them for every query gives the bagged rows the same values
+      const Metadata& md = train_data_->metadata();
+      if (md.query_boundaries.empty()) Log::Fatal("bagging_by_query needs query information");
+      bag_data_cnt_ = bl->BaggingByQueryOnDevice(config_->bagging_seed, config_->bagging_fraction,
+                                                 first ? md.query_boundaries.data() : nullptr, md.num_queries(), first);
+    } else if (balanced_bagging_) {
       bag_data_cnt_ = bl->BalancedBaggingOnDevice(config_->bagging_seed, config_->pos_bagging_fraction, config_->neg_bagging_fraction,
                                                   first ? train_data_->metadata().label.data() : nullptr, first);
     } else {
@@ -154,6 +161,7 @@ void GBDT::Bagging(int iter) {
     Log::Debug("Re-bagging, using %d data to train", bag_data_cnt_);
     return;
   }
+  if (config_->bagging_by_query) Log::Fatal("bagging_by_query needs the B200 tree learner");
   data_size_t cnt = 0;
   const std::vector<label_t>& label = train_data_->metadata().label;
   for (data_size_t i = 0; i < num_data_; ++i) {

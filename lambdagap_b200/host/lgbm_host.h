@@ -341,6 +341,9 @@ class B200TreeLearner : public TreeLearner {
   gbl_learner* handle() const { return handle_; }
   // BaggingSampleStrategy::Bagging drawn on the device (the reference's bag, bit for bit); returns the bag size
   data_size_t BaggingOnDevice(int bagging_seed, double bagging_fraction, bool reset);
+  // bagging_by_query on the device; the boundaries are uploaded when not null
+  data_size_t BaggingByQueryOnDevice(int bagging_seed, double bagging_fraction, const data_size_t* query_boundaries,
+                                     int num_queries, bool reset);
   // BalancedBaggingHelper on the device; `label` is uploaded when not null
   data_size_t BalancedBaggingOnDevice(int bagging_seed, double pos_fraction, double neg_fraction, const label_t* label, bool reset);
   // device-resident pipeline used by GBDT: enqueue the tree, update the scores from the leaf outputs that are

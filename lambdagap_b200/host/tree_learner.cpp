@@ -174,6 +174,13 @@ data_size_t B200TreeLearner::BaggingOnDevice(int bagging_seed, double bagging_fr
   return cnt;
 }
 
+data_size_t B200TreeLearner::BaggingByQueryOnDevice(int bagging_seed, double bagging_fraction, const data_size_t* query_boundaries,
+                                                    int num_queries, bool reset) {
+  int32_t cnt = 0;
+  GblCheck(gbl_learner_bagging_by_query_dev(handle_, bagging_seed, bagging_fraction, query_boundaries, num_queries, reset ? 1 : 0, &cnt));
+  return cnt;
+}
+
 data_size_t B200TreeLearner::BalancedBaggingOnDevice(int bagging_seed, double pos_fraction, double neg_fraction,
                                                      const label_t* label, bool reset) {
   int32_t cnt = 0;

@@ -182,3 +182,24 @@ def test_balanced_bagging(gpu):
     rb, ob = _train_both(X, y, params, 8)
     _compare_models(rb, ob, rtol=1e-5, exact_counts=True)
     np.testing.assert_allclose(ob.train_scores(raw=True), rb.train_scores_raw(), rtol=1e-5, atol=1e-8)
+
+
+def test_bagging_by_query(gpu):
+    """bagging_by_query (src/boosting/bagging.hpp:54-99): whole queries are drawn (generators per block of 1024 queries),
+    their documents form the bag.  The first tree equals the reference's.  Later trees cannot: the reference fills only
+    the in-bag part of bag_data_indices_ in this mode (:88-98), so its out-of-bag score update (gbdt.cpp:505-513) walks
+    stale indices and the training scores of unsampled queries go wrong from the second iteration on.  That is not
+    reproduced; instead every iteration's bag is checked against the restated draw (it depends on the generators only)
+    and the scores against the model's own predictions for ALL rows."""
+    from tests.test_wave_schedule import _reference_bags
+    X, y, q = H.make_ranking(3000, 12, seed=33, min_len=2, max_len=60)  # 3000 queries: three generator blocks
+    params = ("objective=lambdarank num_leaves=15 learning_rate=0.1 min_data_in_leaf=20 bagging_by_query=true "
+              "bagging_fraction=0.7 bagging_freq=1 bagging_seed=4")
+    rb, ob = _train_both(X, y, params, 1, group=q)
+    _compare_models(rb, ob, rtol=1e-5)
+    for _ in range(5):
+        ob.update()
+    counts = [int(t["leaf_count"].sum()) for t in R.parse_model_trees(ob.model_to_string())]
+    want = [int(q[b].sum()) for b in _reference_bags(len(q), 4, 0.7, 6)]
+    assert counts == want and len(set(counts)) > 1
+    np.testing.assert_allclose(ob.train_scores(raw=True), ob.predict(X, raw_score=True), rtol=1e-9, atol=1e-12)
