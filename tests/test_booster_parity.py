@@ -203,3 +203,13 @@ def test_bagging_by_query(gpu):
     want = [int(q[b].sum()) for b in _reference_bags(len(q), 4, 0.7, 6)]
     assert counts == want and len(set(counts)) > 1
     np.testing.assert_allclose(ob.train_scores(raw=True), ob.predict(X, raw_score=True), rtol=1e-9, atol=1e-12)
+
+
+def test_quantized_stochastic_rounding(gpu):
+    """use_quantized_grad with its default stochastic rounding: the per-row random offsets are the reference's host
+    mt19937 arrays (GradientDiscretizer::Init, gradient_discretizer.cpp:16-41; one generator pair per thread block, so
+    both sides run with the same num_threads) rotated by the per-iteration start (:116); trees stay bit-identical."""
+    X, y = H.make_binary(30000, 16, seed=37, nan_frac=0.03, zero_frac=0.2)
+    params = "objective=binary num_leaves=31 learning_rate=0.1 min_data_in_leaf=20 use_quantized_grad=true seed=3"
+    rb, ob = _train_both(X, y, params, 10)
+    _compare_models(rb, ob, rtol=1e-5)
