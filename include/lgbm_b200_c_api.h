@@ -109,6 +109,9 @@ LGBM_B200_EXPORT int LGBM_B200_FindBin(double* values, int num_values, int64_t t
                                        int min_data_in_bin, int min_split_data, int pre_filter, int use_missing,
                                        int zero_as_missing, int32_t out_scalars[5], double* out_upper_bounds, int cap);
 /* not in the reference: the C-ABI learner handle behind a booster (gbl_learner*), for timers and profiling */
+/* test tap (no counterpart in the reference's C API): the parameter string as Config::Set understood it, as `[key: value]`
+ * lines like the parameter block of a model file; needs no GPU */
+LGBM_B200_EXPORT int LGBM_B200_DumpConfig(const char* parameters, int64_t buffer_len, int64_t* out_len, char* out_str);
 LGBM_B200_EXPORT int LGBM_BoosterGetLearnerHandle(BoosterHandle handle, void** out_learner);
 /* not in the reference: raw (unconverted) training scores, device -> host */
 LGBM_B200_EXPORT int LGBM_BoosterGetTrainScoreRaw(BoosterHandle handle, int64_t* out_len, double* out_result);

@@ -21,7 +21,7 @@ LGBM_EXPORTED_SYMBOLS = [
     "LGBM_BoosterPredictForMat", "LGBM_BoosterSaveModelToString", "LGBM_NetworkGetNcclUniqueId",
     "LGBM_NetworkInitWithNccl", "LGBM_NetworkFree", "LGBM_BoosterGetTrainScoreRaw",
     "LGBM_DatasetCreateFromMatWithSample", "LGBM_BoosterGetLearnerHandle", "LGBM_B200_FindBin",
-    "LGBM_BoosterResetParameter", "LGBM_BoosterGetNumClasses", "LGBM_BoosterNumModelPerIteration",
+    "LGBM_B200_DumpConfig", "LGBM_BoosterResetParameter", "LGBM_BoosterGetNumClasses", "LGBM_BoosterNumModelPerIteration",
     "LGBM_BoosterGetNumFeature", "LGBM_BoosterGetLeafValue", "LGBM_BoosterFeatureImportance", "LGBM_BoosterSaveModel",
     "LGBM_BoosterAddValidData", "LGBM_BoosterGetEvalCounts", "LGBM_BoosterGetEvalNames", "LGBM_BoosterGetEval",
 ]
@@ -98,6 +98,19 @@ class Dataset:
         if self.handle:
             lib().LGBM_DatasetFree(self.handle)
             self.handle = None
+
+
+def dump_config(params):
+    """Config::Set of the host layer applied to a parameter string -> dict of the `[key: value]` lines (no GPU needed)."""
+    buf = ctypes.create_string_buffer(4096)
+    n = ctypes.c_int64(0)
+    _check(lib().LGBM_B200_DumpConfig(ctypes.c_char_p(_params(params)), ctypes.c_int64(len(buf)), ctypes.byref(n), buf))
+    out = {}
+    for line in buf.value.decode().split("\n"):
+        if line.startswith("["):
+            k, v = line[1:-1].split(": ", 1) if ": " in line else (line[1:-2], "")
+            out[k] = v
+    return out
 
 
 class Booster:

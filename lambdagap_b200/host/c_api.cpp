@@ -311,6 +311,27 @@ int LGBM_B200_FindBin(double* values, int num_values, int64_t total_sample_cnt, 
   API_END();
 }
 
+int LGBM_B200_DumpConfig(const char* parameters, int64_t buffer_len, int64_t* out_len, char* out_str) {
+  API_BEGIN();
+  // test tap: what Config::Set made of a parameter string, in the `[key: value]` form of the model file's parameter
+  // block (src/io/config_auto.cpp Config::SaveMembersToString), so that it can be compared with the reference's
+  Config c;
+  c.Set(parameters ? parameters : "");
+  std::string metrics;
+  for (size_t i = 0; i < c.metric_types.size(); ++i) metrics += (i ? "," : "") + c.metric_types[i];
+  std::string eval_at;
+  for (size_t i = 0; i < c.eval_at.size(); ++i) eval_at += (i ? "," : "") + std::to_string(c.eval_at[i]);
+  const std::string s = "[objective: " + c.objective + "]\n[metric: " + metrics + "]\n[eval_at: " + eval_at + "]\n[seed: " +
+                        std::to_string(c.seed) + "]\n[data_random_seed: " + std::to_string(c.data_random_seed) +
+                        "]\n[bagging_seed: " + std::to_string(c.bagging_seed) + "]\n[feature_fraction_seed: " +
+                        std::to_string(c.feature_fraction_seed) + "]\n[num_leaves: " + std::to_string(c.num_leaves) +
+                        "]\n[min_data_in_leaf: " + std::to_string(c.min_data_in_leaf) + "]\n[bagging_freq: " +
+                        std::to_string(c.bagging_freq) + "]\n";
+  *out_len = static_cast<int64_t>(s.size()) + 1;
+  if (*out_len <= buffer_len) std::memcpy(out_str, s.c_str(), *out_len);
+  API_END();
+}
+
 int LGBM_BoosterGetLearnerHandle(BoosterHandle handle, void** out_learner) {
   API_BEGIN();
   Booster* b = reinterpret_cast<Booster*>(handle);

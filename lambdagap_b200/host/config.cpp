@@ -88,6 +88,13 @@ static const std::unordered_map<std::string, std::string>& AliasTable() {
       {"metrics", "metric"}, {"metric_types", "metric"},
       {"ndcg_eval_at", "eval_at"}, {"ndcg_at", "eval_at"}, {"map_eval_at", "eval_at"}, {"map_at", "eval_at"},
       {"linear_trees", "linear_tree"},
+      {"pos_sub_row", "pos_bagging_fraction"}, {"pos_subsample", "pos_bagging_fraction"},
+      {"pos_bagging", "pos_bagging_fraction"}, {"neg_sub_row", "neg_bagging_fraction"},
+      {"neg_subsample", "neg_bagging_fraction"}, {"neg_bagging", "neg_bagging_fraction"},
+      {"bagging_fraction_seed", "bagging_seed"}, {"extra_tree", "extra_trees"},
+      {"is_enable_bundle", "enable_bundle"}, {"bundle", "enable_bundle"},
+      {"training_metric", "is_provide_training_metric"}, {"is_training_metric", "is_provide_training_metric"},
+      {"train_metric", "is_provide_training_metric"},
   };
   return t;
 }

@@ -196,3 +196,44 @@ def test_metric_restatement_matches_reference():
         b.update()
     assert b.eval_names() == ["ndcg@1", "ndcg@3", "ndcg@5", "ndcg@10", "ndcg@500"]
     np.testing.assert_allclose(b.eval(0), M.ndcg(b.train_scores(), yr, qb, [1, 3, 5, 10, 500]), rtol=1e-14)
+
+
+def _ref_param_block(params, group=None):
+    from oracle import ref_lgbm as R
+    rng = np.random.default_rng(0)
+    X = rng.normal(size=(400, 4)).astype(np.float32)
+    y = rng.integers(0, 2, size=400).astype(np.float32)
+    ds = R.RefDataset(X, y, group=group, params="verbose=-1")
+    text = R.RefBooster(ds, params + " verbose=-1 min_data_in_leaf=5").model_string()
+    block = text[text.index("parameters:"):]
+    out = {}
+    for line in block.split("\n"):
+        if line.startswith("[") and ": " in line:
+            k, v = line[1:-1].split(": ", 1)
+            out[k] = v
+        elif line.startswith("["):
+            out[line[1:-2].rstrip(":")] = ""
+    return out
+
+
+@pytest.mark.parametrize("params,group", [
+    ("objective=binary seed=7 metric=auc,binary,auc", None),
+    ("objective=regression_l2 metric=mse,l2_root,mae,l2", None),
+    ("objective=mse", None),
+    ("objective=lambdarank ndcg_eval_at=5,1,3 seed=123", [100] * 4),
+    ("objective=lambdarank metric=lambdarank", [100] * 4),
+    ("application=binary num_leaf=7 min_data=9 subsample=0.8 subsample_freq=2 bagging_fraction_seed=77", None),
+])
+def test_host_config_matches_reference(params, group):
+    """Config::Set of the host layer (aliases, metric list with aliases resolved and duplicates dropped, the objective's
+    default metric, sorted eval_at, the seeds derived from `seed`) against the parameter block the reference writes into
+    its model file (Config::SaveMembersToString).  Needs no GPU: LGBM_B200_DumpConfig is a tap on the parser."""
+    from oracle import ref_lgbm as R
+    if not R.available():
+        pytest.skip("oracle/_ref not built")
+    ref = _ref_param_block(params, None if group is None else np.array(group, dtype=np.int32))
+    ours = engine.dump_config(params + " device_type=cuda")
+    for key in ("objective", "metric", "eval_at", "data_random_seed", "bagging_seed", "feature_fraction_seed", "num_leaves",
+                "bagging_freq"):
+        assert ours[key] == ref[key], "%s: ours %r, reference %r" % (key, ours[key], ref[key])
+    assert ours["min_data_in_leaf"] == ("9" if "min_data=9" in params else "20")
