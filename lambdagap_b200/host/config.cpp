@@ -2,6 +2,7 @@
 // Reference: Config::Str2Map / KV2Map / Set (src/io/config.cpp:20-120,255-312), alias table
 // (src/io/config_auto.cpp:10-180), objective aliases (src/io/config.cpp:70-110).
 #include <algorithm>
+#include <cmath>
 #include <cstring>
 #include <sstream>
 
@@ -95,6 +96,22 @@ static const std::unordered_map<std::string, std::string>& AliasTable() {
       {"is_enable_bundle", "enable_bundle"}, {"bundle", "enable_bundle"},
       {"training_metric", "is_provide_training_metric"}, {"is_training_metric", "is_provide_training_metric"},
       {"train_metric", "is_provide_training_metric"},
+      {"mc", "monotone_constraints"},
+      {"monotone_constraint", "monotone_constraints"},
+      {"monotonic_cst", "monotone_constraints"},
+      {"feature_contrib", "feature_contri"},
+      {"fc", "feature_contri"},
+      {"fp", "feature_contri"},
+      {"feature_penalty", "feature_contri"},
+      {"fs", "forcedsplits_filename"},
+      {"forced_splits_filename", "forcedsplits_filename"},
+      {"forced_splits_file", "forcedsplits_filename"},
+      {"forced_splits", "forcedsplits_filename"},
+      {"cat_feature", "categorical_feature"},
+      {"categorical_column", "categorical_feature"},
+      {"cat_column", "categorical_feature"},
+      {"categorical_features", "categorical_feature"},
+      {"num_classes", "num_class"},
   };
   return t;
 }
@@ -276,6 +293,8 @@ void Config::Set(const std::string& parameters) {
   Log::level = verbosity;
 
   // ---- what this learner does not implement fails loudly instead of silently training something else
+  if (objective != "regression" && objective != "binary" && objective != "lambdarank" && objective != "custom")
+    Log::Fatal("objective=%s is not supported by the B200 learner (regression, binary, lambdarank, custom)", objective.c_str());
   if (boosting != "gbdt" && boosting != "gbrt") Log::Fatal("boosting=%s is not supported by the B200 learner (gbdt only)", boosting.c_str());
   if (tree_learner != "serial" && tree_learner != "data" && tree_learner != "data_parallel")
     Log::Fatal("tree_learner=%s is not supported by the B200 learner (serial, data)", tree_learner.c_str());
@@ -294,8 +313,29 @@ void Config::Set(const std::string& parameters) {
   if (max_bin > 255) Log::Fatal("max_bin=%d: the B200 learner stores one byte per cell (max_bin <= 255)", max_bin);
   if (num_leaves < 2) Log::Fatal("num_leaves must be at least 2");
   for (const char* k : {"monotone_constraints", "interaction_constraints", "forcedsplits_filename", "categorical_feature",
-                        "cegb_tradeoff", "cegb_penalty_split", "forcedbins_filename", "max_bin_by_feature"}) {
+                        "cegb_tradeoff", "cegb_penalty_split", "cegb_penalty_feature_lazy", "cegb_penalty_feature_coupled",
+                        "forcedbins_filename", "max_bin_by_feature", "feature_contri", "init_score_filename"}) {
     if (get(k) != nullptr && !get(k)->empty()) Log::Fatal("parameter %s is not supported by the B200 learner", k);
+  }
+  // parameters that would change what is trained must not be ignored silently
+  if (const std::string* v = get("data_sample_strategy")) {
+    if (*v != "bagging") Log::Fatal("data_sample_strategy=%s is not supported by the B200 learner (bagging only)", v->c_str());
+  }
+  if (const std::string* v = get("num_class")) {
+    if (std::stoi(*v) != 1) Log::Fatal("num_class=%s: multiclass training is not supported by the B200 learner", v->c_str());
+  }
+  // ---- Config::CheckParamConflict (src/io/config.cpp:375-460), the parts that touch this learner
+  if (max_depth > 0 && (get("num_leaves") == nullptr || get("num_leaves")->empty())) {
+    const double full_num_leaves = std::pow(2, max_depth);  // a depth limit without num_leaves caps num_leaves
+    if (full_num_leaves < num_leaves) num_leaves = static_cast<int>(full_num_leaves);
+  }
+  if (path_smooth > 1e-15f && min_data_in_leaf < 2) {
+    min_data_in_leaf = 2;
+    Log::Warning("min_data_in_leaf has been increased to 2 because this is required when path smoothing is active.");
+  }
+  if (min_data_in_leaf <= 0 && min_sum_hessian_in_leaf <= 1e-15f) {
+    Log::Warning("Cannot set both min_data_in_leaf and min_sum_hessian_in_leaf to 0. Will set min_data_in_leaf to 1.");
+    min_data_in_leaf = 1;
   }
 }
 

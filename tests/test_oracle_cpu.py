@@ -143,10 +143,14 @@ def test_no_cpu_fallback_fails_loudly():
 
 
 def test_config_rejects_what_the_learner_does_not_implement():
+    """Parameters that would change what is trained are rejected by the parser itself (LGBM_B200_DumpConfig needs no
+    device, so the error cannot be the missing GPU), under their aliases too."""
     for bad in ("boosting=dart", "linear_tree=true", "feature_fraction_bynode=0.5", "max_bin=1023", "device_type=cpu",
-                "monotone_constraints=1,0", "tree_learner=voting"):
-        with pytest.raises(engine.LightGBMError):
-            engine.Dataset(np.zeros((10, 2), dtype=np.float32), np.zeros(10, dtype=np.float32), params=bad + " verbose=-1")
+                "monotone_constraints=1,0", "mc=1,0", "tree_learner=voting", "data_sample_strategy=goss", "boosting=goss",
+                "num_class=3", "fc=0.5,1", "cat_feature=0", "objective=huber", "extra_trees=true"):
+        with pytest.raises(engine.LightGBMError, match="not supported|no CPU path|one byte per cell"):
+            engine.dump_config(bad + " objective=binary device_type=cuda verbose=-1")  # the first occurrence of a key wins
+    engine.dump_config("objective=binary device_type=cuda verbose=-1 feature_fraction=0.5 bagging_fraction=0.5 bagging_freq=1")
 
 
 def test_metric_restatement_matches_reference():
@@ -204,7 +208,7 @@ def _ref_param_block(params, group=None):
     X = rng.normal(size=(400, 4)).astype(np.float32)
     y = rng.integers(0, 2, size=400).astype(np.float32)
     ds = R.RefDataset(X, y, group=group, params="verbose=-1")
-    text = R.RefBooster(ds, params + " verbose=-1 min_data_in_leaf=5").model_string()
+    text = R.RefBooster(ds, params + " verbose=-1").model_string()
     block = text[text.index("parameters:"):]
     out = {}
     for line in block.split("\n"):
@@ -223,6 +227,10 @@ def _ref_param_block(params, group=None):
     ("objective=lambdarank ndcg_eval_at=5,1,3 seed=123", [100] * 4),
     ("objective=lambdarank metric=lambdarank", [100] * 4),
     ("application=binary num_leaf=7 min_data=9 subsample=0.8 subsample_freq=2 bagging_fraction_seed=77", None),
+    ("objective=binary max_depth=3", None),                       # a depth limit without num_leaves caps num_leaves at 2^depth
+    ("objective=binary max_depth=3 num_leaves=20", None),
+    ("objective=binary path_smooth=1.5 min_data_in_leaf=1", None),  # path smoothing needs min_data_in_leaf >= 2
+    ("objective=binary min_data_in_leaf=0 min_sum_hessian_in_leaf=0", None),
 ])
 def test_host_config_matches_reference(params, group):
     """Config::Set of the host layer (aliases, metric list with aliases resolved and duplicates dropped, the objective's
@@ -234,6 +242,5 @@ def test_host_config_matches_reference(params, group):
     ref = _ref_param_block(params, None if group is None else np.array(group, dtype=np.int32))
     ours = engine.dump_config(params + " device_type=cuda")
     for key in ("objective", "metric", "eval_at", "data_random_seed", "bagging_seed", "feature_fraction_seed", "num_leaves",
-                "bagging_freq"):
+                "bagging_freq", "min_data_in_leaf"):
         assert ours[key] == ref[key], "%s: ours %r, reference %r" % (key, ours[key], ref[key])
-    assert ours["min_data_in_leaf"] == ("9" if "min_data=9" in params else "20")
