@@ -244,3 +244,64 @@ def test_host_config_matches_reference(params, group):
     for key in ("objective", "metric", "eval_at", "data_random_seed", "bagging_seed", "feature_fraction_seed", "num_leaves",
                 "bagging_freq", "min_data_in_leaf"):
         assert ours[key] == ref[key], "%s: ours %r, reference %r" % (key, ours[key], ref[key])
+
+
+@pytest.mark.parametrize("ds_params", [
+    "max_bin=255", "max_bin=15", "max_bin=63 min_data_in_bin=10", "max_bin=255 zero_as_missing=true",
+    "max_bin=255 use_missing=false", "max_bin=7 min_data_in_bin=1", "max_bin=255 feature_pre_filter=false",
+])
+def test_host_bin_mapper_edge_columns_against_reference(ds_params):
+    """BinMapper::FindBin (host restatement, no GPU) against the unmodified reference on columns chosen to hit its
+    branches: few distinct values, heavy zeros, NaN-rich, negative-only, constants, huge ranges, values straddling zero,
+    under several dataset parameters (max_bin, min_data_in_bin, zero_as_missing, use_missing, feature_pre_filter)."""
+    from oracle import ref_lgbm as R
+    if not R.available():
+        pytest.skip("oracle/_ref not built")
+    rng = np.random.default_rng(5)
+    n = 4000
+    cols = [
+        rng.normal(size=n),                                              # continuous
+        rng.integers(0, 5, size=n).astype(np.float64),                   # few distinct values incl. zero
+        np.where(rng.random(n) < 0.9, 0.0, rng.normal(size=n)),          # 90 % zeros
+        np.where(rng.random(n) < 0.3, np.nan, rng.normal(size=n)),       # NaN-rich
+        -np.abs(rng.normal(size=n)) - 0.5,                               # negative only
+        np.exp(rng.normal(size=n) * 4),                                  # huge positive range
+        np.round(rng.normal(size=n), 1),                                 # a few hundred distinct values around zero
+        np.where(rng.random(n) < 0.5, np.nan, 0.0),                      # NaN or zero only
+        np.full(n, 3.25),                                                # constant
+        rng.integers(-3, 4, size=n).astype(np.float64) * 1e-3,           # tiny magnitudes around zero
+        np.where(rng.random(n) < 0.02, rng.normal(size=n), 0.0),         # almost all zeros (pre-filter candidate)
+    ]
+    X = np.stack(cols, axis=1)
+    y = rng.integers(0, 2, size=n).astype(np.float32)
+    ds = R.RefDataset(X, y, params=ds_params + " verbose=-1 min_data_in_leaf=20")
+    ref_by_col = {}
+    for i in range(ds.num_used_features()):
+        info = ds.feature_info(i)
+        ref_by_col[info["real_index"]] = info
+    kw = dict(max_bin=255, min_data_in_bin=3, pre_filter=True, use_missing=True, zero_as_missing=False)
+    for tok in ds_params.split():
+        k, v = tok.split("=")
+        if k == "max_bin":
+            kw["max_bin"] = int(v)
+        elif k == "min_data_in_bin":
+            kw["min_data_in_bin"] = int(v)
+        elif k == "zero_as_missing":
+            kw["zero_as_missing"] = v == "true"
+        elif k == "use_missing":
+            kw["use_missing"] = v == "true"
+        elif k == "feature_pre_filter":
+            kw["pre_filter"] = v == "true"
+    for c in range(X.shape[1]):
+        col = X[:, c]
+        vals = col[(np.abs(col) > 1e-35) | np.isnan(col)]
+        got = engine.find_bin(vals, n, min_split_data=20, **kw)
+        if c not in ref_by_col:
+            assert got["is_trivial"], "column %d: the reference dropped it as trivial" % c
+            continue
+        info = ref_by_col[c]
+        assert not got["is_trivial"], "column %d" % c
+        for key in ("num_bin", "missing_type", "default_bin", "most_freq_bin"):
+            assert got[key] == info[key], "column %d %s: %s vs %s" % (c, key, got[key], info[key])
+        real = info["num_bin"] - (1 if info["missing_type"] == 2 else 0)
+        np.testing.assert_array_equal(got["upper_bounds"][:real], info["upper_bounds"][:real], err_msg="column %d" % c)
