@@ -95,6 +95,39 @@ def test_ndcg_matches_restatement(gpu):
         np.testing.assert_allclose(got, M.ndcg(s, y, qb, eval_at), rtol=1e-14)
 
 
+def test_device_metrics_reproduce_golden(gpu):
+    """The committed fixtures hold the reference's own scores and the metric values it computed on them
+    (tests/golden/make_golden_metrics.py): the device metrics must give the same numbers -- AUC exactly."""
+    import os
+    golden = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    z = np.load(os.path.join(golden, "metrics_binary.npz"))
+    buf = _dev(z["prob"])
+    for k, name in enumerate(z["names"]):
+        m = capi.Metric(str(name), z["label"], sigmoid=0.0)  # the fixture's scores are probabilities already
+        got = m.eval(buf.data_ptr())[0]
+        m.free()
+        if name == "binary_logloss":
+            np.testing.assert_allclose(got, z["values"][k], rtol=1e-11)
+        else:
+            assert got == z["values"][k], name
+    z = np.load(os.path.join(golden, "metrics_regression.npz"))
+    buf = _dev(z["score"])
+    for k, name in enumerate(z["names"]):
+        m = capi.Metric(str(name), z["label"])
+        got = m.eval(buf.data_ptr())[0]
+        m.free()
+        if name == "auc":
+            assert got == z["values"][k]
+        else:
+            np.testing.assert_allclose(got, z["values"][k], rtol=1e-11)
+    z = np.load(os.path.join(golden, "metrics_rank.npz"))
+    qb = np.concatenate(([0], np.cumsum(z["group"]))).astype(np.int32)
+    buf = _dev(z["score"])
+    m = capi.Metric("ndcg", z["label"], query_boundaries=qb, eval_at=[int(k) for k in z["eval_at"]])
+    np.testing.assert_allclose(m.eval(buf.data_ptr()), z["values"], rtol=1e-13)
+    m.free()
+
+
 def test_metric_argument_errors(gpu):
     y = np.zeros(10, dtype=np.float32)
     with pytest.raises(capi.GblError, match="query information"):

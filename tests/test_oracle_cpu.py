@@ -305,3 +305,22 @@ def test_host_bin_mapper_edge_columns_against_reference(ds_params):
             assert got[key] == info[key], "column %d %s: %s vs %s" % (c, key, got[key], info[key])
         real = info["num_bin"] - (1 if info["missing_type"] == 2 else 0)
         np.testing.assert_array_equal(got["upper_bounds"][:real], info["upper_bounds"][:real], err_msg="column %d" % c)
+
+
+def test_metric_restatement_reproduces_golden():
+    """oracle/oracle_metrics.py on the committed fixtures (tests/golden/metrics_*.npz, written by
+    tests/golden/make_golden_metrics.py from the reference's own scores and metric values): no reference library needed."""
+    from oracle import oracle_metrics as M
+    z = np.load(os.path.join(ROOT, "tests", "golden", "metrics_binary.npz"))
+    assert list(z["names"]) == ["binary_logloss", "auc", "binary_error"]
+    np.testing.assert_allclose(M.binary_logloss(z["prob"], z["label"]), z["values"][0], rtol=1e-13)
+    assert M.auc(z["prob"], z["label"]) == z["values"][1]
+    assert M.binary_error(z["prob"], z["label"]) == z["values"][2]
+    z = np.load(os.path.join(ROOT, "tests", "golden", "metrics_regression.npz"))
+    assert list(z["names"]) == ["l2", "rmse", "l1", "auc"]
+    np.testing.assert_allclose([M.l2(z["score"], z["label"]), M.rmse(z["score"], z["label"]), M.l1(z["score"], z["label"])],
+                               z["values"][:3], rtol=1e-13)
+    assert M.auc(z["score"], z["label"]) == z["values"][3]
+    z = np.load(os.path.join(ROOT, "tests", "golden", "metrics_rank.npz"))
+    qb = np.concatenate(([0], np.cumsum(z["group"])))
+    np.testing.assert_allclose(M.ndcg(z["score"], z["label"], qb, list(z["eval_at"])), z["values"], rtol=1e-14)
