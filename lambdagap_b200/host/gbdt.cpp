@@ -101,19 +101,33 @@ void GBDT::Init(const Config* config, const Dataset* train_data, ObjectiveFuncti
 // make the result independent of the number of threads, so this sequential version draws the reference's bag.
 // bagging.hpp:146-147: plain bagging, or balanced bagging when a positive / negative fraction is set and the objective
 // counts positive rows (binary only: ObjectiveFunction::NumPositiveData is 0 elsewhere)
-bool GBDT::BaggingEnabled(const Config* config, bool* balanced) const {
-  data_size_t num_pos = 0;
-  if (objective_function_ != nullptr && std::string(objective_function_->GetName()) == "binary") {
-    for (label_t l : train_data_->metadata().label) num_pos += l > 0 ? 1 : 0;
+// The labels are walked only when a positive / negative fraction asks for balanced bagging, and then once
+// (BinaryLogloss::Init counts them once too, binary_objective.hpp:58-72); the per-iteration guard below is O(1) like
+// the reference's (bagging.hpp:29-33 tests counters and flags only).
+data_size_t GBDT::NumPositiveData() const {
+  if (num_pos_ < 0) {
+    data_size_t num_pos = 0;
+    if (objective_function_ != nullptr && std::string(objective_function_->GetName()) == "binary") {
+      for (label_t l : train_data_->metadata().label) num_pos += l > 0 ? 1 : 0;
+    }
+    num_pos_ = num_pos;
   }
-  *balanced = (config->pos_bagging_fraction < 1.0 || config->neg_bagging_fraction < 1.0) && num_pos > 0;
+  return num_pos_;
+}
+
+bool GBDT::BaggingEnabled(const Config* config, bool* balanced) const {
+  *balanced = (config->pos_bagging_fraction < 1.0 || config->neg_bagging_fraction < 1.0) && NumPositiveData() > 0;
   return (config->bagging_fraction < 1.0 || *balanced) && config->bagging_freq > 0;
 }
 
 void GBDT::Bagging(int iter) {
   if (!bagging_ready_) {
+    if (bagging_off_) return;  // decided at the first iteration / in ResetConfig, not per iteration
     bool balanced = false;
-    if (!BaggingEnabled(config_, &balanced)) return;
+    if (!BaggingEnabled(config_, &balanced)) {
+      bagging_off_ = true;
+      return;
+    }
     balanced_bagging_ = balanced;
   }
   B200TreeLearner* bl = dynamic_cast<B200TreeLearner*>(tree_learner_.get());
@@ -126,8 +140,7 @@ void GBDT::Bagging(int iter) {
     bag_neg_used_ = config_->neg_bagging_fraction;
     bag_freq_used_ = config_->bagging_freq;
     if (balanced_bagging_) {
-      data_size_t num_pos = 0;
-      for (label_t l : train_data_->metadata().label) num_pos += l > 0 ? 1 : 0;
+      const data_size_t num_pos = NumPositiveData();
       bag_data_cnt_ = static_cast<data_size_t>(num_pos * config_->pos_bagging_fraction) +
                       static_cast<data_size_t>((num_data_ - num_pos) * config_->neg_bagging_fraction);
     } else {
@@ -282,6 +295,7 @@ void GBDT::ResetConfig(const Config* config) {
   // and the current bag; anything else starts over (generators re-seeded, next iteration re-bags)
   bool balanced = false;
   const bool enabled = BaggingEnabled(config, &balanced);
+  bagging_off_ = false;  // re-decided at the next iteration
   if (enabled && bagging_ready_ && bag_fraction_used_ == config->bagging_fraction && bag_freq_used_ == config->bagging_freq &&
       bag_pos_used_ == config->pos_bagging_fraction && bag_neg_used_ == config->neg_bagging_fraction)
     return;

@@ -422,6 +422,9 @@ class GBDT {
   double bag_fraction_used_ = 1.0, bag_pos_used_ = 1.0, bag_neg_used_ = 1.0;
   bool balanced_bagging_ = false;
   bool BaggingEnabled(const Config* config, bool* balanced) const;
+  data_size_t NumPositiveData() const;  // counted once, on first need
+  mutable data_size_t num_pos_ = -1;
+  bool bagging_off_ = false;            // "no bagging" decided once, so GBDT::Bagging is O(1) per iteration
   int bag_freq_used_ = 0;
   data_size_t bag_data_cnt_ = 0;
   bool need_re_bagging_ = false;
