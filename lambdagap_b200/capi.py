@@ -9,7 +9,9 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "liblambdagap_b200.so")
+# GBL_LIB_DIR: an alternative directory holding both libraries (A/B timing of two builds in one process launch each)
+LIB_DIR = os.environ.get("GBL_LIB_DIR") or os.path.join(_HERE, "lib")
+LIB_PATH = os.path.join(LIB_DIR, "liblambdagap_b200.so")
 
 MISSING_NONE, MISSING_ZERO, MISSING_NAN = 0, 1, 2
 OBJ_REGRESSION_L2, OBJ_BINARY, OBJ_LAMBDARANK = 0, 1, 2

@@ -176,6 +176,7 @@ static LearnerParams make_params(const Learner* L) {
 
 static void setup_peer(Learner* L);
 static void teardown_peer(Learner* L);
+static void apply_gh_window_to_stream(Learner* L);
 
 static void drop_graph(Learner* L) {
   if (L->graph_exec != nullptr) {
@@ -213,18 +214,18 @@ static void free_tree_buffers(Learner* L) {
 }
 
 // Row records.  The histogram kernel gathers, per row and 32-feature tile, the tile's bins and the row's gradient
-// pair.  DRAM serves 64-byte bursts, so two separate gathers (a 32-byte bin sector here, an 8-byte pair there) cost
-// two bursts -- measured 181 B of DRAM traffic per row against 40 B algorithmic on the Higgs shape.  A record keeps
-// them together, one block per tile:
-//   [32 bytes of bins of tile 0][pair + padding] [32 bytes of bins of tile 1][pair + padding] ...   (64 B per tile)
-// (float mode: int2 fixed point; quantized: int8 [hess, grad]); every tile block has its own copy of the pair
-// because every tile is accumulated by its own CTAs.  With a single tile whose unused tail has room for the pair
-// (quantized Higgs: 28 bins + 2 bytes) the record is just the 32-byte sector.  The records belong to the learner,
-// not the dataset: gradients are per learner, and several learners may share one dataset.
-static void record_layout(int num_features, int num_tiles, bool quant, int* gh_off, int* tile_stride, int* stride) {
-  const int gh_bytes = quant ? 2 : 8;
-  const int inside = static_cast<int>(round_up(num_features, gh_bytes));
-  if (num_tiles == 1 && inside + gh_bytes <= kTile) {
+// pair.  Float mode: DRAM serves whole bursts, so two separate gathers (a 32-byte bin sector here, an 8-byte pair
+// there, out of an 8 x num_data byte array that does not stay in L2) cost two bursts -- measured 181 B of DRAM traffic
+// per row against 40 B algorithmic on the Higgs shape.  A float-mode record keeps them together, one block per tile:
+//   [32 bytes of bins of tile 0][int2 fixed-point pair + padding] [32 bytes of bins of tile 1][pair + padding] ...
+// (64 B per tile; every tile block has its own copy of the pair because every tile is accumulated by its own CTAs).
+// The records belong to the learner, not the dataset: gradients are per learner, several learners may share a dataset.
+// Quantized mode: the int8 pairs are 2 bytes per row -- an array that stays in L2 (21 MB on the Higgs shape) -- so they
+// live in gh_q and the "records" are the dataset's read-only row mirror itself (32 bytes per row and tile, no copy).
+// With a single tile whose unused tail has room for the pair (at most 24 features) the record is just the 32-byte sector.
+static void record_layout(int num_features, int num_tiles, int* gh_off, int* tile_stride, int* stride) {
+  const int inside = static_cast<int>(round_up(num_features, 8));
+  if (num_tiles == 1 && inside + 8 <= kTile) {
     *gh_off = inside;
     *tile_stride = kTile;
   } else {
@@ -237,20 +238,32 @@ static void record_layout(int num_features, int num_tiles, bool quant, int* gh_o
 static void build_records(Learner* L) {
   const Dataset* ds = L->ds;
   const bool quant = L->cfg.use_quantized_grad != 0;
+  if (quant) {
+    cudaFree(L->rec);
+    L->rec = nullptr;
+    L->rec_quant = true;
+    L->dev.rec = ds->row_bins;  // never written in this mode
+    L->dev.rec_stride = ds->row_stride;
+    L->dev.tile_stride = kTile;
+    L->dev.gh_off = 0;
+    apply_gh_window_to_stream(L);
+    return;
+  }
   int gh_off = 0, tile_stride = 0, stride = 0;
-  record_layout(ds->num_features, ds->num_tiles, quant, &gh_off, &tile_stride, &stride);
-  if (L->rec != nullptr && L->rec_quant == quant) return;
+  record_layout(ds->num_features, ds->num_tiles, &gh_off, &tile_stride, &stride);
+  if (L->rec != nullptr && !L->rec_quant) return;
   cudaFree(L->rec);
   L->rec = nullptr;
   GBL_CUDA(cudaMalloc(&L->rec, static_cast<size_t>(ds->num_data) * stride + 64));
   GBL_CUDA(cudaMemsetAsync(L->rec, 0, static_cast<size_t>(ds->num_data) * stride + 64, L->stream));
   launch_build_records(L->rec, stride, tile_stride, ds->row_bins, ds->row_stride, static_cast<int>(ds->num_data), L->stream);
   GBL_CUDA(cudaStreamSynchronize(L->stream));
-  L->rec_quant = quant;
+  L->rec_quant = false;
   L->dev.rec = L->rec;
   L->dev.rec_stride = stride;
   L->dev.tile_stride = tile_stride;
   L->dev.gh_off = gh_off;
+  apply_gh_window_to_stream(L);
 }
 
 // (re)allocates everything that depends on the config.
@@ -544,6 +557,65 @@ static void setup_peer(Learner* L) {
   L->peer = true;
 }
 
+// Quantized mode: the int8 gradient pairs (2 bytes per row) are gathered by row id in every wave.  The row records
+// stream through L2 at several hundred MB per launch and would evict them (measured: +13 B of DRAM traffic per
+// gathered row), so the array is pinned with a persisting access-policy window -- on the learner's stream for the
+// host-driven loop and on every kernel node of the tree graph.
+static bool gh_window(const Learner* L, cudaAccessPolicyWindow* w) {
+  if (!L->cfg.use_quantized_grad || L->gh_q == nullptr) return false;
+  if (const char* e = std::getenv("GBL_L2_PERSIST")) {
+    if (e[0] == '0') return false;
+  }
+  int max_window = 0, max_persist = 0;
+  cudaDeviceGetAttribute(&max_window, cudaDevAttrMaxAccessPolicyWindowSize, L->ds->device);
+  cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, L->ds->device);
+  const size_t bytes = sizeof(short) * static_cast<size_t>(L->ds->num_data);
+  if (max_window <= 0 || max_persist <= 0) return false;
+  const size_t win = std::min(bytes, static_cast<size_t>(max_window));
+  w->base_ptr = L->gh_q;
+  w->num_bytes = win;
+  // more bytes than may persist: pin the fraction that fits
+  w->hitRatio = static_cast<float>(std::min(1.0, static_cast<double>(max_persist) / static_cast<double>(win)));
+  w->hitProp = cudaAccessPropertyPersisting;
+  w->missProp = cudaAccessPropertyStreaming;
+  return true;
+}
+
+static void apply_gh_window_to_stream(Learner* L) {
+  cudaAccessPolicyWindow w{};
+  cudaStreamAttrValue v{};
+  if (gh_window(L, &w)) {
+    int max_persist = 0;
+    cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, L->ds->device);
+    size_t cur = 0;
+    cudaDeviceGetLimit(&cur, cudaLimitPersistingL2CacheSize);
+    const size_t want = std::min(static_cast<size_t>(max_persist), w.num_bytes);
+    if (cur < want) cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want);
+    v.accessPolicyWindow = w;
+  } else {
+    v.accessPolicyWindow.num_bytes = 0;  // no window
+  }
+  cudaStreamSetAttribute(L->stream, cudaStreamAttributeAccessPolicyWindow, &v);
+  cudaGetLastError();  // a device without the feature keeps working without it
+}
+
+static void apply_gh_window_to_graph(Learner* L, cudaGraph_t g) {
+  cudaAccessPolicyWindow w{};
+  if (!gh_window(L, &w)) return;
+  size_t n = 0;
+  if (cudaGraphGetNodes(g, nullptr, &n) != cudaSuccess || n == 0) return;
+  std::vector<cudaGraphNode_t> nodes(n);
+  if (cudaGraphGetNodes(g, nodes.data(), &n) != cudaSuccess) return;
+  cudaKernelNodeAttrValue v{};
+  v.accessPolicyWindow = w;
+  for (cudaGraphNode_t nd : nodes) {
+    cudaGraphNodeType ty;
+    if (cudaGraphNodeGetType(nd, &ty) == cudaSuccess && ty == cudaGraphNodeTypeKernel)
+      cudaGraphKernelNodeSetAttribute(nd, cudaKernelNodeAttributeAccessPolicyWindow, &v);
+  }
+  cudaGetLastError();
+}
+
 // ---- the three parts of a tree.  prologue: root histogram, root scan, first wave selected.  wave: split every
 // node of the wave, histograms of the smaller children, scan of all children, next wave selected.  epilogue: replay.
 static void enqueue_prologue(Learner* L, cudaStream_t s, cudaGraphConditionalHandle cond, int use_cond) {
@@ -709,6 +781,8 @@ static void build_graph(Learner* L) {
     GBL_CUDA(cudaStreamBeginCaptureToGraph(s, graph, &loop, nullptr, 1, cudaStreamCaptureModeThreadLocal));
     enqueue_epilogue(L, s);
     GBL_CUDA(cudaStreamEndCapture(s, &got));
+    apply_gh_window_to_graph(L, graph);
+    apply_gh_window_to_graph(L, body);
     GBL_CUDA(cudaGraphInstantiate(&L->graph_exec, graph, 0));
     L->graph_cond = cond;
   } catch (...) {

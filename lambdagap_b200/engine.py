@@ -10,7 +10,7 @@ import numpy as np
 from . import capi
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-HOST_LIB_PATH = os.path.join(_HERE, "lib", "liblgbm_b200.so")
+HOST_LIB_PATH = os.path.join(capi.LIB_DIR, "liblgbm_b200.so")
 C_API_DTYPE_FLOAT32, C_API_DTYPE_FLOAT64, C_API_DTYPE_INT32 = 0, 1, 2
 
 LGBM_EXPORTED_SYMBOLS = [
