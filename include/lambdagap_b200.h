@@ -283,7 +283,9 @@ GBL_API int gbl_learner_get_profile(gbl_learner* learner, gbl_profile* out, int3
  * cannot take cudaMalloc's device-wide synchronisation.  The per-CTA scratch lives in a static device array inside
  * the library (16.25 KB per GPU, held until process exit), so the call performs no allocation of any kind; the
  * caller supplies every buffer: `indices_dev` (NULL = rows 0..num_indices-1), `out_indices_dev[num_indices]`,
- * `out_left_count_dev[1]`, all on the dataset's device.  Limits and rules: at most 16,777,216 rows per call (more is
+ * `out_left_count_dev[1]`, all on the dataset's device.  `indices_dev` and `out_indices_dev` must not overlap (the
+ * partition is not in place; an overlapping call is refused with -1) and every index must be a row of the dataset --
+ * the caller guarantees that, the indices are not range-checked.  Limits and rules: at most 16,777,216 rows per call (more is
  * refused with -1); all calls on one GPU share the scratch, so calls that overlap on the GPU race -- issue them
  * one after another; the first call made on a device also resolves the scratch address and should come before any
  * stream capture.  Asynchronous on `stream` (NULL = default stream). */
@@ -312,6 +314,11 @@ typedef struct gbl_objective_config {
 GBL_API int gbl_objective_create(const gbl_objective_config* config, int64_t num_data, const float* label_host,
                                  const float* weight_host, const int32_t* query_boundaries_host,
                                  int32_t num_queries, int32_t device_id, gbl_objective** out);
+/* BinaryLogloss::Init sums the numbers of positive / negative rows over machines before it derives need_train and the
+ * is_unbalance label weights (src/objective/binary_objective.hpp:73-101, Network::GlobalSyncUpBySum at :75-77).  The
+ * objective is created from one rank's rows; the data-parallel host layer reduces the two counts over ranks and hands the
+ * global numbers in here.  No effect on other objectives. */
+GBL_API int gbl_objective_set_label_counts(gbl_objective* obj, int64_t num_positive, int64_t num_negative);
 GBL_API int gbl_objective_free(gbl_objective* obj);
 /* ObjectiveFunction::GetGradients(score, gradients, hessians) (objective_function.h:37), device pointers */
 GBL_API int gbl_objective_get_gradients(gbl_objective* obj, const double* score_dev, float* gradients_dev,

@@ -91,7 +91,7 @@ EXPORTED_SYMBOLS = [
     "gbl_learner_stream", "gbl_learner_set_profiling", "gbl_learner_get_profile", "gbl_learner_timer_record",
     "gbl_learner_timer_elapsed_ms",
     "gbl_objective_create", "gbl_objective_free", "gbl_objective_get_gradients", "gbl_objective_boost_from_score",
-    "gbl_objective_is_constant_hessian",
+    "gbl_objective_is_constant_hessian", "gbl_objective_set_label_counts",
     "gbl_metric_create", "gbl_metric_free", "gbl_metric_num_outputs", "gbl_metric_eval",
     "gbl_device_malloc", "gbl_device_free", "gbl_memcpy_h2d", "gbl_memcpy_d2h", "gbl_device_fill_f64",
     "gbl_device_synchronize", "gbl_partition_rows_noalloc",

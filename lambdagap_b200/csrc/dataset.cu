@@ -249,8 +249,10 @@ int gbl_dataset_create_from_mat_f32(const gbl_feature_meta* metas, int32_t num_f
     GBL_CUDA(cudaMalloc(&chunk_dev, sizeof(float) * rows_per_chunk * num_total_columns));
     for (int64_t r0 = 0; r0 < num_data; r0 += rows_per_chunk) {
       const int64_t rows = std::min(rows_per_chunk, num_data - r0);
+      // cudaMemcpyDefault: the matrix may also live in device (or managed) memory -- a caller that produced it on the
+      // GPU hands it over without a round trip through the host
       GBL_CUDA(cudaMemcpy(chunk_dev, values_host + r0 * num_total_columns, sizeof(float) * rows * num_total_columns,
-                          cudaMemcpyHostToDevice));
+                          cudaMemcpyDefault));
       dim3 grid(static_cast<unsigned>((rows + 255) / 256), num_features);
       GBL_LAUNCH(value_to_bin_kernel, grid, 256, 0, 0, chunk_dev, r0, rows, num_total_columns, ds->meta_dev, off_dev,
                  bounds_dev, num_features, ds->stage, ds->stage_stride);

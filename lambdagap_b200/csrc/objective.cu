@@ -47,10 +47,10 @@ __global__ void __launch_bounds__(256) binary_gradients_kernel(const double* __r
   }
 }
 
-static void init_binary(Objective* o, const float* label, const float* weight) {
-  // BinaryLogloss::Init, binary_objective.hpp:58-101
-  long long pos = 0, neg = 0;
-  for (int64_t i = 0; i < o->num_data; ++i) (label[i] > 0 ? pos : neg)++;
+// BinaryLogloss::Init, binary_objective.hpp:73-101: need_train and the is_unbalance label weights from the numbers of
+// positive / negative rows.  With sharded rows the reference sums the two counts over machines first (:75-77); the
+// data-parallel host layer does the same and hands the global counts in through gbl_objective_set_label_counts.
+static void set_binary_label_weights(Objective* o, long long pos, long long neg) {
   o->need_train = !(pos == 0 || neg == 0);
   o->label_weight[0] = 1.0;
   o->label_weight[1] = 1.0;
@@ -64,6 +64,13 @@ static void init_binary(Objective* o, const float* label, const float* weight) {
     }
   }
   o->label_weight[1] *= o->cfg.scale_pos_weight;
+}
+
+static void init_binary(Objective* o, const float* label, const float* weight) {
+  // BinaryLogloss::Init, binary_objective.hpp:58-101
+  long long pos = 0, neg = 0;
+  for (int64_t i = 0; i < o->num_data; ++i) (label[i] > 0 ? pos : neg)++;
+  set_binary_label_weights(o, pos, neg);
   // BoostFromScore, :139-166
   double suml = 0.0, sumw = 0.0;
   if (weight != nullptr) {
@@ -180,6 +187,15 @@ int gbl_objective_create(const gbl_objective_config* config, int64_t num_data, c
   if (out == nullptr) fatal("gbl_objective_create: null argument");
   *out = reinterpret_cast<gbl_objective*>(
       objective_create(config, num_data, label_host, weight_host, query_boundaries_host, num_queries, device_id));
+  GBL_API_END();
+}
+
+int gbl_objective_set_label_counts(gbl_objective* obj, int64_t num_positive, int64_t num_negative) {
+  GBL_API_BEGIN();
+  Objective* o = reinterpret_cast<Objective*>(obj);
+  if (o == nullptr) fatal("gbl_objective_set_label_counts: null objective");
+  if (num_positive < 0 || num_negative < 0) fatal("gbl_objective_set_label_counts: negative count");
+  if (o->cfg.kind == GBL_OBJ_BINARY) set_binary_label_weights(o, num_positive, num_negative);
   GBL_API_END();
 }
 

@@ -176,6 +176,14 @@ int gbl_partition_rows_noalloc(const gbl_dataset* ds_, int32_t feature, uint32_t
     fatal("gbl_partition_rows_noalloc: %d rows exceed the fixed scratch of this entry point (at most %d rows per call); "
           "use the learner, which sizes its own scratch", num_indices, kNoAllocMaxRows);
   if (indices_dev == nullptr && num_indices > ds->num_data) fatal("gbl_partition_rows_noalloc: more rows than the dataset holds");
+  if (indices_dev != nullptr && num_indices > 0) {
+    // the scatter pass reads `indices` while other CTAs already write `out`: an in-place (or overlapping) call would
+    // silently corrupt the result
+    const uintptr_t a = reinterpret_cast<uintptr_t>(indices_dev), b = reinterpret_cast<uintptr_t>(out_indices_dev);
+    const uintptr_t bytes = sizeof(int32_t) * static_cast<uintptr_t>(num_indices);
+    if (a < b + bytes && b < a + bytes)
+      fatal("gbl_partition_rows_noalloc: indices_dev and out_indices_dev overlap; the partition is not in place, pass two distinct buffers");
+  }
   DeviceGuard guard(ds->device);
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   int* scratch = noalloc_scratch_for_current_device();  // first call on this device resolves the address

@@ -87,6 +87,25 @@ class Dataset:
         if group is not None:
             self.set_field("group", np.asarray(group, dtype=np.int32))
 
+    @classmethod
+    def from_pointer(cls, ptr, nrow, ncol, label=None, group=None, params=None, bin_sample=None, num_total_rows=None):
+        """Row-major float32 matrix given by address (host or DEVICE memory: the C-ABI layer copies with
+        cudaMemcpyDefault); the bin mappers come from `bin_sample` (a host matrix), which is required here."""
+        self = cls.__new__(cls)
+        self.n, self.f = int(nrow), int(ncol)
+        self.handle = ctypes.c_void_p()
+        S = np.ascontiguousarray(bin_sample, dtype=np.float32)
+        _check(lib().LGBM_DatasetCreateFromMatWithSample(
+            ctypes.c_void_p(int(ptr)), ctypes.c_int(C_API_DTYPE_FLOAT32), ctypes.c_int32(self.n), ctypes.c_int32(self.f),
+            ctypes.c_int(1), S.ctypes.data_as(ctypes.c_void_p), ctypes.c_int32(S.shape[0]),
+            ctypes.c_int64(num_total_rows if num_total_rows is not None else self.n),
+            ctypes.c_char_p(_params(params)), ctypes.byref(self.handle)))
+        if label is not None:
+            self.set_field("label", np.asarray(label, dtype=np.float32))
+        if group is not None:
+            self.set_field("group", np.asarray(group, dtype=np.int32))
+        return self
+
     def set_field(self, name, arr):
         arr = np.ascontiguousarray(arr)
         dt = {np.dtype(np.float32): C_API_DTYPE_FLOAT32, np.dtype(np.float64): C_API_DTYPE_FLOAT64,

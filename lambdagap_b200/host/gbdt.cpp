@@ -80,6 +80,7 @@ void GBDT::Init(const Config* config, const Dataset* train_data, ObjectiveFuncti
   bool is_constant_hessian = false;
   if (objective_function_ != nullptr) {
     objective_function_->Init(train_data->metadata(), num_data_, device_id_);
+    if (comm != nullptr) objective_function_->SyncLabelCounts(train_data->metadata(), comm);
     is_constant_hessian = objective_function_->IsConstantHessian();
   }
   tree_learner_.reset(TreeLearner::CreateTreeLearner(comm != nullptr ? "data" : config->tree_learner == "serial" ? "serial" : config->tree_learner,

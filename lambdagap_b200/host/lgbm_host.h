@@ -272,6 +272,8 @@ class ObjectiveFunction {
   // with a communicator: label / weight sums are reduced over ranks first (BinaryLogloss::BoostFromScore does
   // Network::GlobalSyncUpBySum, binary_objective.hpp:157-160), so every rank starts from the global init score
   double BoostFromScoreGlobal(const Metadata& metadata, gbl_comm* comm) const;
+  // with a communicator: positive / negative row counts summed over ranks (binary_objective.hpp:75-77)
+  void SyncLabelCounts(const Metadata& metadata, gbl_comm* comm) const;
   bool IsConstantHessian() const;
   const char* GetName() const { return name_.c_str(); }
   std::string ToString() const;

@@ -302,6 +302,16 @@ double ObjectiveFunction::BoostFromScore(int /*class_id*/) const {
   return v;
 }
 
+void ObjectiveFunction::SyncLabelCounts(const Metadata& md, gbl_comm* comm) const {
+  // BinaryLogloss::Init, binary_objective.hpp:75-77: cnt_positive / cnt_negative are summed over machines before the
+  // is_unbalance label weights are derived -- otherwise every rank would weight its rows by its own shard's ratio
+  if (name_ != "binary" || comm == nullptr) return;
+  double cnt[2] = {0.0, 0.0};
+  for (label_t l : md.label) cnt[l > 0 ? 0 : 1] += 1.0;
+  GblCheck(gbl_comm_allreduce_host_f64(comm, cnt, 2, 0));
+  GblCheck(gbl_objective_set_label_counts(handle_, static_cast<int64_t>(cnt[0]), static_cast<int64_t>(cnt[1])));
+}
+
 double ObjectiveFunction::BoostFromScoreGlobal(const Metadata& md, gbl_comm* comm) const {
   if (name_ == "lambdarank") return 0.0;
   double sums[2] = {0.0, 0.0};  // suml, sumw

@@ -13,14 +13,25 @@ from tests import helpers as H
 pytestmark = pytest.mark.gpu
 
 
-def _assert_same_trees(ours, ref, leaf_rtol):
+def _assert_same_trees(ours, ref, leaf_rtol, empty_bin_ties=0.0):
+    """empty_bin_ties: fraction of a tree's thresholds that may differ from the reference's although the split is the
+    same one (float mode only).  When a node holds no row in a bin, the two thresholds on either side of that bin
+    separate its rows identically: same children, same counts, same sums.  With exact integer sums that is an exact
+    tie here (resolved like the reference's sequential scan resolves ties); in the reference the empty most-frequent
+    bin carries the rounding residue of `leaf total - sum of the other bins` (Dataset::FixHistogram), so its two gains
+    differ in the last bits and either may win.  Everything that depends on the rows -- feature, default direction,
+    children, every leaf / internal count, leaf values -- is still asserted equal."""
     ot, rt = R.parse_model_trees(ours), R.parse_model_trees(ref)
     assert len(ot) == len(rt) > 0
     for k, (a, b) in enumerate(zip(ot, rt)):
         assert a["num_leaves"] == b["num_leaves"], "tree %d" % k
         for key in ("split_feature", "left_child", "right_child", "decision_type", "leaf_count", "internal_count"):
             np.testing.assert_array_equal(a[key], b[key], err_msg="tree %d %s" % (k, key))
-        np.testing.assert_array_equal(a["threshold"], b["threshold"], err_msg="tree %d threshold" % k)
+        if empty_bin_ties > 0.0:
+            differ = np.mean(a["threshold"] != b["threshold"])
+            assert differ <= empty_bin_ties, "tree %d: %.1f %% of the thresholds differ" % (k, 100 * differ)
+        else:
+            np.testing.assert_array_equal(a["threshold"], b["threshold"], err_msg="tree %d threshold" % k)
         np.testing.assert_allclose(a["leaf_value"], b["leaf_value"], rtol=leaf_rtol, atol=1e-12, err_msg="tree %d" % k)
     return ot
 
@@ -138,3 +149,60 @@ def test_mslr_shape_full_size_properties(gpu):
     per_query = np.add.reduceat(g, qb[:-1])
     scale = np.add.reduceat(np.abs(g), qb[:-1]) + 1e-30
     assert np.max(np.abs(per_query) / scale) < 1e-4  # fp32 accumulation of +l / -l in different orders
+
+
+def test_higgs_shape_full_size_float_matches_reference(gpu):
+    """The configuration bench.py's headline is quoted on, at its own size and in its own mode: bench.py's Higgs-shape
+    matrix (10.5 M x 28, seed 42), float gradients, num_leaves=255, 3 iterations against the unmodified reference CPU
+    learner.  SURVEY.md 8(c): identical chosen splits (feature, threshold, default direction, children, leaf counts),
+    leaf values within 1e-5."""
+    import bench
+    cfg = dict(bench.HIGGS)
+    X, y = bench.gen_block(cfg, 0, cfg["rows"])
+    n, iters = X.shape[0], 3
+    params = cfg["params"] + " verbose=-1"
+    ods = engine.Dataset(X, y, params="max_bin=255 verbose=-1")
+    ob = engine.Booster(ods, params + " device_type=cuda")
+    for _ in range(iters):
+        ob.update()
+    ours = ob.model_to_string()
+    s = ob.train_scores(raw=True)
+    ob.free()
+    ods.free()
+    rds = R.RefDataset(X, y, params="max_bin=255 verbose=-1 force_col_wise=true")
+    rb = R.RefBooster(rds, params + " device_type=cpu force_col_wise=true deterministic=true")
+    for _ in range(iters):
+        rb.update()
+    trees = _assert_same_trees(ours, rb.model_string(), leaf_rtol=1e-5)
+    for t in trees:
+        assert t["num_leaves"] == 255 and int(t["leaf_count"].sum()) == n
+    np.testing.assert_allclose(s, rb.train_scores_raw(), rtol=1e-5, atol=1e-9)
+
+
+@pytest.mark.parametrize("target", ["ndcg", "lambdagap-x"])
+def test_mslr_shape_full_size_matches_reference(gpu, target):
+    """Config 3 at full size against the reference itself: ~3.77 M documents x 136 features in 31 531 queries,
+    lambdarank with num_leaves=255, 2 iterations.  The lambda gradients replay the CPU's fp32 pair order, so the chosen
+    splits are expected to be identical; leaf values and scores within 1e-5."""
+    X, y, group = H.make_ranking(31531, 136, seed=43, min_len=1, max_len=1251, zero_frac=0.3, median_len=95)
+    n, iters = X.shape[0], 2
+    params = ("objective=lambdarank lambdarank_target=%s lambdarank_truncation_level=30 num_leaves=255 learning_rate=0.1 "
+              "min_data_in_leaf=20 verbose=-1" % target)
+    ods = engine.Dataset(X, y, group=group, params="max_bin=255 verbose=-1")
+    ob = engine.Booster(ods, params + " device_type=cuda")
+    for _ in range(iters):
+        ob.update()
+    ours = ob.model_to_string()
+    s = ob.train_scores(raw=True)
+    ob.free()
+    ods.free()
+    rds = R.RefDataset(X, y, group=group, params="max_bin=255 verbose=-1 force_col_wise=true")
+    rb = R.RefBooster(rds, params + " device_type=cpu force_col_wise=true deterministic=true")
+    for _ in range(iters):
+        rb.update()
+    # ~30 % of the columns are zero-inflated: deep nodes without a single zero row produce the empty-bin tie described
+    # in _assert_same_trees (seen: 2 of 254 thresholds of one tree, +1e-35 here against -1e-35 in the reference)
+    trees = _assert_same_trees(ours, rb.model_string(), leaf_rtol=1e-5, empty_bin_ties=0.02)
+    for t in trees:
+        assert int(t["leaf_count"].sum()) == n
+    np.testing.assert_allclose(s, rb.train_scores_raw(), rtol=1e-5, atol=1e-9)

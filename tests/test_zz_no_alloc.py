@@ -79,4 +79,7 @@ def test_noalloc_partition_matches_learner_twice(gpu):
     # sizes beyond the fixed scratch are refused with a clear error, nothing is launched
     with pytest.raises(capi.GblError, match="at most"):
         capi.partition_rows_noalloc(ds, 0, 3, True, None, (1 << 24) + 1, out, cnt)
+    # an in-place call (input list == output buffer) is refused too: the scatter pass reads the input while writing the output
+    with pytest.raises(capi.GblError, match="overlap"):
+        capi.partition_rows_noalloc(ds, rec2["feature"], rec2["threshold_bin"], rec2["default_left"], idx, len(sub), idx, cnt)
     ds.free()
