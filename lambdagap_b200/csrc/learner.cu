@@ -8,6 +8,8 @@
 // WHILE conditional node around the wave (GBL_USE_GRAPH=0, stage profiling and the data-parallel learner drive the
 // waves from the host, reading the small tree state back once per wave).  The reference CUDA learner synchronises with the host
 // twice per split (src/treelearner/cuda/cuda_single_gpu_tree_learner.cpp:246-325).
+#include <unistd.h>
+
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
@@ -467,10 +469,13 @@ static void setup_peer(Learner* L) {
   // mapped only once per peer process -- a second learner's control block in the same region could not be opened)
   GBL_CUDA(cudaMalloc(&L->xchg_ctl, kCtlAlloc));
   GBL_CUDA(cudaMemset(L->xchg_ctl, 0, kCtlBytes));
-  // 16 int64 words per rank: two 64-byte IPC handles (pool, control block)
+  // kWords int64 words per rank: two 64-byte IPC handles (pool, control block), then process id, the two raw device
+  // pointers and the device ordinal -- ranks that share this process (one Booster driving several GPUs from host
+  // threads) cannot open each other's IPC handles; they use the raw pointers after enabling peer access instead
+  constexpr int kWords = 20;
   long long* table_dev = nullptr;
-  GBL_CUDA(cudaMalloc(&table_dev, sizeof(long long) * 16 * R));
-  GBL_CUDA(cudaMemset(table_dev, 0, sizeof(long long) * 16 * R));
+  GBL_CUDA(cudaMalloc(&table_dev, sizeof(long long) * kWords * R));
+  GBL_CUDA(cudaMemset(table_dev, 0, sizeof(long long) * kWords * R));
   GBL_CUDA(cudaDeviceSynchronize());  // the control block is zero before any peer can learn its handle
   cudaIpcMemHandle_t hp, hc;
   bool ok = want;
@@ -479,12 +484,18 @@ static void setup_peer(Learner* L) {
   cudaGetLastError();
   static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
   if (ok) {
-    GBL_CUDA(cudaMemcpy(table_dev + 16 * me, &hp, 64, cudaMemcpyHostToDevice));
-    GBL_CUDA(cudaMemcpy(table_dev + 16 * me + 8, &hc, 64, cudaMemcpyHostToDevice));
+    long long mine[kWords];
+    std::memcpy(mine, &hp, 64);
+    std::memcpy(mine + 8, &hc, 64);
+    mine[16] = static_cast<long long>(getpid());
+    mine[17] = static_cast<long long>(reinterpret_cast<uintptr_t>(L->hist_pool));
+    mine[18] = static_cast<long long>(reinterpret_cast<uintptr_t>(L->xchg_ctl));
+    mine[19] = L->ds->device;
+    GBL_CUDA(cudaMemcpy(table_dev + kWords * me, mine, sizeof(mine), cudaMemcpyHostToDevice));
   }
-  comm_allreduce_i64(c, table_dev, static_cast<size_t>(16) * R, RedOp::kSum, s);
+  comm_allreduce_i64(c, table_dev, static_cast<size_t>(kWords) * R, RedOp::kSum, s);
   GBL_CUDA(cudaStreamSynchronize(s));
-  std::vector<long long> table(static_cast<size_t>(16) * R);
+  std::vector<long long> table(static_cast<size_t>(kWords) * R);
   GBL_CUDA(cudaMemcpy(table.data(), table_dev, sizeof(long long) * table.size(), cudaMemcpyDeviceToHost));
   cudaFree(table_dev);
   std::vector<void*> pools(R, nullptr), ctls(R, nullptr);
@@ -493,13 +504,31 @@ static void setup_peer(Learner* L) {
   for (int r = 0; r < R && ok; ++r) {
     if (r == me) continue;
     cudaIpcMemHandle_t a, b;
-    std::memcpy(&a, &table[16 * r], 64);
-    std::memcpy(&b, &table[16 * r + 8], 64);
+    std::memcpy(&a, &table[kWords * r], 64);
+    std::memcpy(&b, &table[kWords * r + 8], 64);
     bool zero = true;
-    for (int k = 0; k < 16; ++k) zero = zero && table[16 * r + k] == 0;
+    for (int k = 0; k < kWords; ++k) zero = zero && table[kWords * r + k] == 0;
     if (zero) {  // that rank could not export its memory
       ok = false;
       break;
+    }
+    if (table[kWords * r + 16] == static_cast<long long>(getpid())) {
+      // same process: the peer's allocations are ordinary pointers of this address space
+      const int peer_dev = static_cast<int>(table[kWords * r + 19]);
+      int can = 0;
+      if (cudaDeviceCanAccessPeer(&can, L->ds->device, peer_dev) != cudaSuccess || !can) {
+        ok = false;
+        break;
+      }
+      const cudaError_t e = cudaDeviceEnablePeerAccess(peer_dev, 0);
+      if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) {
+        ok = false;
+        break;
+      }
+      cudaGetLastError();
+      pools[r] = reinterpret_cast<void*>(static_cast<uintptr_t>(table[kWords * r + 17]));
+      ctls[r] = reinterpret_cast<void*>(static_cast<uintptr_t>(table[kWords * r + 18]));
+      continue;
     }
     void* pp = nullptr;
     void* pc = nullptr;

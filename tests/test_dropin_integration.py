@@ -1,0 +1,136 @@
+"""The drop-in the north star asks for, compiled and run: integration/_ref/lib_lightgbm.so is the REFERENCE library
+(its GBDT, Config, Dataset, objectives, sampling strategies, Tree, model I/O, C API -- built from /root/reference by
+integration/Makefile) with its TreeLearner factory re-pointed so that `device_type=cuda` creates the B200 learner
+(integration/b200_tree_learner.cpp, a subclass of the reference's own TreeLearner, include/LightGBM/tree_learner.h:27-115).
+Here the reference's own LGBM_BoosterCreate(... device_type=cuda) in that library must grow the trees that the
+unmodified reference grows with device_type=cpu (oracle/_ref) on the same inputs: bit-exact with quantized gradients,
+identical splits and 1e-5 on values in float mode.  The drop-in runs in a process of its own (tests/dropin_runner.py)."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from lambdagap_b200 import capi
+from oracle import ref_lgbm as R
+from tests import helpers as H
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+DROPIN = os.path.join(ROOT, "integration", "_ref", "lib_lightgbm.so")
+
+
+def _run_dropin(tmp_path, X, y, params, iters, group=None, dataset_params="max_bin=255 verbose=-1"):
+    if not os.path.exists(DROPIN):
+        pytest.fail("integration/_ref/lib_lightgbm.so missing: run __graft_entry__.build() where /root/reference exists")
+    src, dst = str(tmp_path / "in.npz"), str(tmp_path / "out.npz")
+    arrays = dict(X=X, y=y, params=np.array(params), dataset_params=np.array(dataset_params), iters=np.array(iters))
+    if group is not None:
+        arrays["group"] = group
+    np.savez(src, **arrays)
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "dropin_runner.py"), src, dst], capture_output=True, text=True,
+                       timeout=600)
+    assert r.returncode == 0, "drop-in run failed:\n" + r.stdout[-2000:] + r.stderr[-4000:]
+    z = np.load(dst)
+    return str(z["model"]), z["scores"]
+
+
+def _run_reference(X, y, params, iters, group=None, dataset_params="max_bin=255 verbose=-1"):
+    ds = R.RefDataset(X, y, group=group, params=dataset_params + " force_col_wise=true")
+    b = R.RefBooster(ds, params + " device_type=cpu force_col_wise=true deterministic=true")
+    for _ in range(iters):
+        b.update()
+    return b.model_string(), b.train_scores()
+
+
+def _assert_models(ours, ref, leaf_rtol, count_exact=True):
+    ot, rt = R.parse_model_trees(ours), R.parse_model_trees(ref)
+    assert len(ot) == len(rt) > 0
+    for k, (a, b) in enumerate(zip(ot, rt)):
+        assert a["num_leaves"] == b["num_leaves"], "tree %d" % k
+        keys = ["split_feature", "left_child", "right_child", "decision_type"]
+        if count_exact:
+            keys += ["leaf_count", "internal_count"]
+        for key in keys:
+            np.testing.assert_array_equal(a[key], b[key], err_msg="tree %d %s" % (k, key))
+        np.testing.assert_array_equal(a["threshold"], b["threshold"], err_msg="tree %d threshold" % k)
+        np.testing.assert_allclose(a["leaf_value"], b["leaf_value"], rtol=leaf_rtol, atol=1e-12, err_msg="tree %d" % k)
+
+
+CASES = {
+    "binary_quantized": ("objective=binary num_leaves=63 learning_rate=0.1 min_data_in_leaf=20 use_quantized_grad=true "
+                         "stochastic_rounding=false verbose=-1 num_threads=4", 1e-9),
+    "binary_quantized_stochastic": ("objective=binary num_leaves=31 learning_rate=0.1 use_quantized_grad=true "
+                                    "stochastic_rounding=true seed=7 verbose=-1 num_threads=4", 1e-9),
+    "binary_float": ("objective=binary num_leaves=63 learning_rate=0.1 min_data_in_leaf=20 verbose=-1 num_threads=4", 1e-5),
+    "regression_l2": ("objective=regression num_leaves=63 learning_rate=0.1 lambda_l2=0.5 verbose=-1 num_threads=4", 1e-5),
+    "regression_l1_renew": ("objective=regression_l1 num_leaves=31 learning_rate=0.1 verbose=-1 num_threads=4", 1e-5),
+    "bagging": ("objective=binary num_leaves=31 learning_rate=0.1 bagging_fraction=0.7 bagging_freq=1 bagging_seed=5 "
+                "verbose=-1 num_threads=4", 1e-5),
+    "goss": ("objective=binary num_leaves=31 learning_rate=0.1 data_sample_strategy=goss top_rate=0.2 other_rate=0.1 "
+             "verbose=-1 num_threads=4", 1e-5),
+    "feature_fraction": ("objective=binary num_leaves=31 learning_rate=0.1 feature_fraction=0.6 feature_fraction_seed=9 "
+                         "verbose=-1 num_threads=4", 1e-5),
+}
+
+
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_dropin_equals_reference_cpu(gpu, tmp_path, name):
+    params, rtol = CASES[name]
+    X, y = H.make_binary(120_000, 20, seed=3, nan_frac=0.02, zero_frac=0.2)
+    if name.startswith("regression"):
+        y = (X[:, 0] * 0.5 + np.nan_to_num(X[:, 2]) + 0.1 * np.random.default_rng(1).normal(size=len(y))).astype(np.float32)
+    iters = 4
+    ours, s_ours = _run_dropin(tmp_path, X, y, params + " device_type=cuda", iters)
+    ref, s_ref = _run_reference(X, y, params, iters)
+    _assert_models(ours, ref, rtol)
+    np.testing.assert_allclose(s_ours, s_ref, rtol=max(rtol, 1e-7), atol=1e-9)
+
+
+def test_dropin_multiclass(gpu, tmp_path):
+    """num_class trees per iteration: GBDT calls TreeLearner::Train once per class with offset gradient pointers."""
+    rng = np.random.default_rng(5)
+    X = rng.normal(size=(60_000, 12)).astype(np.float32)
+    y = (np.argmax(X[:, :3] + 0.3 * rng.normal(size=(len(X), 3)), axis=1)).astype(np.float32)
+    params = "objective=multiclass num_class=3 num_leaves=31 learning_rate=0.1 verbose=-1 num_threads=4"
+    ours, s_ours = _run_dropin(tmp_path, X, y, params + " device_type=cuda", 3)
+    ref, s_ref = _run_reference(X, y, params, 3)
+    _assert_models(ours, ref, 1e-5)
+    np.testing.assert_allclose(s_ours, s_ref, rtol=1e-5, atol=1e-9)
+
+
+@pytest.mark.parametrize("target", ["ndcg", "lambdagap-x"])
+def test_dropin_lambdarank(gpu, tmp_path, target):
+    """The fork's lambdarank targets through the reference's own objective (host gradients) and the B200 learner."""
+    X, y, group = H.make_ranking(1500, 24, seed=11)
+    params = ("objective=lambdarank lambdarank_target=%s lambdarank_truncation_level=10 num_leaves=31 learning_rate=0.1 "
+              "min_data_in_leaf=20 verbose=-1 num_threads=4" % target)
+    ours, s_ours = _run_dropin(tmp_path, X, y, params + " device_type=cuda", 4, group=group)
+    ref, s_ref = _run_reference(X, y, params, 4, group=group)
+    _assert_models(ours, ref, 1e-5)
+    np.testing.assert_allclose(s_ours, s_ref, rtol=1e-5, atol=1e-9)
+
+
+def test_dropin_num_gpu_shards_rows_inside_one_booster(gpu, tmp_path):
+    """SURVEY 8(e) route B: device_type=cuda num_gpu=2 in ONE Booster (the reference refuses num_gpu != 1,
+    src/treelearner/tree_learner.cpp:46-50).  Integer histogram sums make the 2-GPU trees equal the CPU's."""
+    if capi.device_count() < 2:
+        pytest.skip("needs two GPUs (run with gpurun --gpus 2)")
+    X, y = H.make_binary(200_000, 20, seed=4)
+    for extra, rtol in ((" use_quantized_grad=true stochastic_rounding=false", 1e-9), ("", 1e-5)):
+        params = "objective=binary num_leaves=63 learning_rate=0.1 verbose=-1 num_threads=4" + extra
+        ours, s_ours = _run_dropin(tmp_path, X, y, params + " device_type=cuda num_gpu=2", 4)
+        ref, s_ref = _run_reference(X, y, params, 4)
+        _assert_models(ours, ref, rtol)
+        np.testing.assert_allclose(s_ours, s_ref, rtol=max(rtol, 1e-7), atol=1e-9)
+
+
+def test_dropin_refuses_what_the_learner_does_not_implement(gpu, tmp_path):
+    X, y = H.make_binary(5_000, 6, seed=1)
+    src, dst = str(tmp_path / "in.npz"), str(tmp_path / "out.npz")
+    np.savez(src, X=X, y=y, params=np.array("objective=binary device_type=cuda extra_trees=true verbose=-1"),
+             dataset_params=np.array("max_bin=255 verbose=-1"), iters=np.array(1))
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "dropin_runner.py"), src, dst], capture_output=True, text=True,
+                       timeout=300)
+    assert r.returncode != 0 and "extra_trees is not supported" in (r.stdout + r.stderr)
