@@ -550,6 +550,23 @@ def shape_leg(ctx, which, steps, warmup):
     return out
 
 
+def reference_cuda_leg(rows, timeout_s=240):
+    script = os.path.join(ROOT, "scripts", "ref_cuda_leg.py")
+    if not os.path.exists(os.path.join(ROOT, "oracle", "_ref_cuda", "lib_lightgbm.so")):
+        return {"unavailable": "oracle/_ref_cuda/lib_lightgbm.so not built (oracle/Makefile.ref_cuda needs /root/reference)"}
+    try:
+        r = subprocess.run([sys.executable, script, "--steps", "10", "--warmup", "3", "--rows", str(rows)], capture_output=True,
+                           text=True, timeout=timeout_s)
+        for line in reversed(r.stdout.strip().split("\n")):
+            if line.startswith("{"):
+                return json.loads(line)
+        return {"error": ("rc=%d " % r.returncode) + (r.stderr or r.stdout)[-300:]}
+    except subprocess.TimeoutExpired:
+        return {"error": "timed out after %d s" % timeout_s}
+    except Exception as ex:
+        return {"error": str(ex)[:300]}
+
+
 # ------------------------------------------------------------------------------------------------ our arm
 def main():
     ap = argparse.ArgumentParser()
@@ -756,6 +773,12 @@ def main():
     ds.free()
     del X, y
 
+    # ---- context, never instead of --impl reference: the reference's own CUDA tree learner (the kernel to beat) on the
+    # same box and workload, in a process of its own (oracle/_ref_cuda, scripts/ref_cuda_leg.py)
+    ref_cuda = None
+    if rank == 0 and world == 1 and secondary and not args.quantized:
+        ref_cuda = reference_cuda_leg(cfg["rows"])
+
     parity = None
     reg = None
     shapes = None
@@ -790,7 +813,8 @@ def main():
                "schedule": {"waves_per_tree": prof["waves"] / max(1, prof["trees"]),
                             "expansions_per_tree": prof["expansions"] / max(1, prof["trees"]),
                             "splits_per_tree": prof["splits"] / max(1, prof["trees"])},
-               "quantized_mode": quant_leg, "parity": parity, "reg100m": reg, "other_shapes": shapes}
+               "quantized_mode": quant_leg, "parity": parity, "reg100m": reg, "other_shapes": shapes,
+               "reference_cuda": ref_cuda}
         print(json.dumps(out), flush=True)
     if world > 1:
         dist.barrier()

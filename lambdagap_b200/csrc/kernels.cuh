@@ -11,6 +11,8 @@ struct PeerX {
   float* const* maxbuf;     // [num_ranks] every rank's (max |g|, max |h|) deposit array ([num_ranks][2] floats each)
   unsigned* epoch;          // own barrier sequence number
   unsigned* dead;           // own sticky "a barrier timed out" flag
+  unsigned* done;           // own count of exchange-kernel CTAs that have finished their share
+  unsigned* go;             // own "every rank has arrived" word: CTA 0 of the exchange kernel releases the others with it
   int rank;
   int pad;
   long long timeout_cycles;  // bound of every barrier wait (SM clocks)
@@ -104,8 +106,8 @@ void launch_build_records(uint8_t* rec, int rec_stride, int tile_stride, const u
 // bag_count_dev != nullptr: the bag size is read on the device (device-drawn bags change size without a new graph)
 void launch_tree_begin(const LearnerDev& d, const int* bag_indices, int bag_count, const int* bag_count_dev, cudaStream_t s);
 // exchange.cu
-void launch_xchg_barrier(const LearnerDev& d, cudaStream_t s);
-void launch_xchg_reduce(const LearnerDev& d, int is_root, cudaStream_t s);
+void launch_xchg_wave(const LearnerDev& d, int is_root, cudaStream_t s);  // barrier + in-place sum over ranks + barrier
+bool xchg_fused_enabled();  // GBL_XCHG_FUSED=1: the exchange as one kernel instead of three launches
 void launch_xchg_max(const LearnerDev& d, cudaStream_t s);
 // bagging.cu
 void launch_bag_seed(unsigned* state, int nblk, int seed, cudaStream_t s);

@@ -442,7 +442,8 @@ static void learner_free(Learner* L) {
 // same point (learner creation / reset_config).  Handles travel through one int64 all-reduce (each rank fills its own
 // 128 bytes of a zeroed table).  If any rank cannot map a peer (ranks sharing one process, no peer access) all ranks
 // keep the NCCL path.
-constexpr size_t kCtlFlagsOff = 0, kCtlMaxOff = 256, kCtlEpochOff = 1024, kCtlDeadOff = 1028, kCtlBytes = 2048, kCtlAlloc = 2u << 20;
+constexpr size_t kCtlFlagsOff = 0, kCtlMaxOff = 256, kCtlEpochOff = 1024, kCtlDeadOff = 1028, kCtlDoneOff = 1032, kCtlGoOff = 1036, kCtlBytes = 2048,
+                 kCtlAlloc = 2u << 20;
 
 static void teardown_peer(Learner* L) {
   for (void* p : L->peer_pool_maps) cudaIpcCloseMemHandle(p);
@@ -577,6 +578,8 @@ static void setup_peer(Learner* L) {
   x.maxbuf = reinterpret_cast<float* const*>(L->xchg_tables + 2 * R);
   x.epoch = reinterpret_cast<unsigned*>(L->xchg_ctl + kCtlEpochOff);
   x.dead = reinterpret_cast<unsigned*>(L->xchg_ctl + kCtlDeadOff);
+  x.done = reinterpret_cast<unsigned*>(L->xchg_ctl + kCtlDoneOff);
+  x.go = reinterpret_cast<unsigned*>(L->xchg_ctl + kCtlGoOff);
   x.rank = me;
   double timeout_s = 60.0;
   if (const char* e = std::getenv("GBL_PEER_TIMEOUT_S")) timeout_s = std::max(0.001, std::atof(e));
@@ -677,9 +680,7 @@ static void enqueue_prologue(Learner* L, cudaStream_t s, cudaGraphConditionalHan
   if (multi) {
     StageTimer tm(L, s, kStageComm);
     if (L->peer) {
-      launch_xchg_barrier(d, s);
-      launch_xchg_reduce(d, 1, s);
-      launch_xchg_barrier(d, s);
+      launch_xchg_wave(d, 1, s);
     } else {
       comm_allreduce_i64(L->comm, L->hist_pool, static_cast<size_t>(d.slot_stride), RedOp::kSum, s);
     }
@@ -713,9 +714,7 @@ static void enqueue_wave_back(Learner* L, cudaStream_t s, cudaGraphConditionalHa
   if (multi && L->peer) {
     // the same sum over NVLink peer memory, sized on the device (exchange.cu): no host involvement, graph-capturable
     StageTimer tm(L, s, kStageComm);
-    launch_xchg_barrier(d, s);
-    launch_xchg_reduce(d, 0, s);
-    launch_xchg_barrier(d, s);
+    launch_xchg_wave(d, 0, s);
   } else if (multi && num_slots > 0) {
     // the wave's histograms + (smaller, larger) row counts in one all-reduce; replaces Network::ReduceScatter of
     // data_parallel_tree_learner.cpp:285-297 and the count sync of :457-458
@@ -870,7 +869,8 @@ static void train_async(Learner* L, const float* grad_dev, const float* hess_dev
 // waves): prologue (tree_begin, [bagged index copy], maxabs, scales, histogram, root_init, scan, select) + 6 per
 // wave + the replay
 static long long kernels_of_tree(const Learner* L, const TreeState& t) {
-  const long long xchg = L->peer ? 6 + 3LL * t.waves : 0;  // max exchange (3), root sum (3), 3 per wave
+  const long long per_xchg = xchg_fused_enabled() ? 1 : 3;  // barrier / reduce / barrier, or the one-kernel form
+  const long long xchg = L->peer ? 1 + per_xchg * (1 + t.waves) : 0;  // max exchange, root sum, one exchange per wave
   return (L->bag_indices != nullptr ? 8 : 7) + 6LL * t.waves + 1 + xchg +
          ((L->cfg.use_quantized_grad && L->cfg.quant_train_renew_leaf) ? 3 : 0);
 }
