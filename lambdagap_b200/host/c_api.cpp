@@ -44,6 +44,12 @@ struct Booster {
       config.tree_learner = "serial";
     }
     if (g_num_machines > 1 && config.tree_learner == "serial") config.tree_learner = "data";
+    // num_gpu > 1 in ONE Booster is implemented by the drop-in library (integration/, B200TreeLearner over row shards);
+    // this stand-alone layer drives one GPU per Booster and scales with one rank per GPU (LGBM_NetworkInitWithNccl)
+    if (config.num_gpu > 1 && g_num_machines <= 1)
+      Log::Warning("num_gpu=%d is ignored by this library: this Booster trains on one GPU.  Use one rank per GPU "
+                   "(LGBM_NetworkInitWithNccl + tree_learner=data) or integration/_ref/lib_lightgbm.so, which shards the "
+                   "rows over num_gpu GPUs inside one Booster", config.num_gpu);
     objective.reset(ObjectiveFunction::CreateObjectiveFunction(config.objective, config));
     boosting.reset(new GBDT());
     boosting->Init(&config, train_data, objective.get(), g_num_machines > 1 ? g_comm : nullptr);
