@@ -58,7 +58,7 @@ typedef struct gbl_feature_meta {
   int32_t default_bin;   /* BinMapper::GetDefaultBin(): bin of value 0.0 */
   int32_t most_freq_bin; /* BinMapper::GetMostFreqBin() */
   int32_t real_index;    /* Dataset::RealFeatureIndex(inner): original column, used for split tie-breaks */
-  int32_t reserved;
+  int32_t monotone_type; /* FeatureMetainfo::monotone_type: -1 / 0 / +1 (config.monotone_constraints), 0 by default */
   double penalty;        /* FeatureMetainfo::penalty (feature_contri), 1.0 by default */
 } gbl_feature_meta;
 
@@ -166,6 +166,14 @@ GBL_API int gbl_learner_free(gbl_learner* learner);
 /* TreeLearner::ResetConfig (tree_learner.h:49) */
 GBL_API int gbl_learner_reset_config(gbl_learner* learner, const gbl_learner_config* config);
 /* ColSampler::is_feature_used_bytree (src/treelearner/col_sampler.hpp); NULL = all features */
+/* Monotone constraints, method "basic" (src/treelearner/monotone_constraints.hpp:465-514: every leaf carries one
+ * [min, max] output interval, inherited from its parent and tightened at a split on a constrained feature to the
+ * mid-point of the two child outputs).  `enabled` mirrors `!config.monotone_constraints.empty()`: the reference then
+ * takes its USE_MC code path for EVERY feature (outputs clamped to the leaf's interval, gain from the clamped outputs,
+ * feature_histogram.hpp:740-797), whatever the feature's own type; the per-feature types come with the dataset
+ * (gbl_feature_meta.monotone_type).  `monotone_penalty`: config.h:532, applied to the gain of splits on constrained
+ * features by depth (monotone_constraints.hpp:357-366).  Call before training; drops the captured tree. */
+GBL_API int gbl_learner_set_monotone(gbl_learner* learner, int32_t enabled, double monotone_penalty);
 GBL_API int gbl_learner_set_feature_mask(gbl_learner* learner, const int8_t* is_feature_used_host);
 /* TreeLearner::SetBaggingData (tree_learner.h:75): sorted row subset used for the next trees; NULL/0 = all rows */
 GBL_API int gbl_learner_set_bagging_data(gbl_learner* learner, const int32_t* used_indices_host, int32_t num_used);

@@ -51,11 +51,11 @@ void B200TreeLearner::Release() {
 // Everything the device learner does not implement is refused here, loudly, instead of being trained differently.
 void B200TreeLearner::CheckConfig() const {
   if (config_->linear_tree) Log::Fatal("B200 tree learner: linear_tree is not supported");
-  if (!config_->monotone_constraints.empty()) {
-    for (int8_t c : config_->monotone_constraints) {
-      if (c != 0) Log::Fatal("B200 tree learner: monotone_constraints are not supported");
-    }
-  }
+  // monotone constraints: the reference's default method ("basic": one output interval per leaf) is implemented on the
+  // device; "intermediate" / "advanced" re-tighten OTHER leaves after a split and are not
+  if (!config_->monotone_constraints.empty() && config_->monotone_constraints_method != std::string("basic"))
+    Log::Fatal("B200 tree learner: monotone_constraints_method=%s is not supported (basic is)",
+               config_->monotone_constraints_method.c_str());
   if (config_->extra_trees) Log::Fatal("B200 tree learner: extra_trees is not supported");
   if (config_->feature_fraction_bynode < 1.0) Log::Fatal("B200 tree learner: feature_fraction_bynode < 1 is not supported");
   if (!config_->interaction_constraints.empty()) Log::Fatal("B200 tree learner: interaction_constraints are not supported");
@@ -126,7 +126,8 @@ void B200TreeLearner::BuildDeviceData() {
     metas[f].default_bin = static_cast<int>(m->GetDefaultBin());
     metas[f].most_freq_bin = static_cast<int>(m->GetMostFreqBin());
     metas[f].real_index = train_data_->RealFeatureIndex(f);
-    metas[f].reserved = 0;
+    // FeatureMetainfo::monotone_type (feature_histogram.hpp:1440-1444): indexed by the ORIGINAL column
+    metas[f].monotone_type = config_->monotone_constraints.empty() ? 0 : static_cast<int>(config_->monotone_constraints[train_data_->RealFeatureIndex(f)]);
     // feature_contri (FeatureMetainfo::penalty, feature_histogram.hpp:1435-1439)
     const int real = train_data_->RealFeatureIndex(f);
     metas[f].penalty = config_->feature_contri.empty() ? 1.0 : config_->feature_contri[real];
@@ -170,6 +171,7 @@ void B200TreeLearner::CreateLearners() {
     if (gbl_learner_create(s.dataset, &c, s.comm, &s.learner) != 0) throw std::runtime_error(gbl_last_error());
     s.records.resize(config_->num_leaves);
   });
+  PushMonotone(true);
 }
 
 void B200TreeLearner::InitQuantRandom() {
@@ -205,6 +207,15 @@ void B200TreeLearner::InitQuantRandom() {
   quant_start_engine_ = std::mt19937(config_->seed);
   quant_start_dist_ = std::uniform_int_distribution<data_size_t>(0, n);
   quant_random_ready_ = true;
+}
+
+// `!monotone_constraints.empty()` selects the reference's USE_MC code path for every feature (feature_histogram.hpp:246-260)
+void B200TreeLearner::PushMonotone(bool force) {
+  const bool on = !config_->monotone_constraints.empty();
+  if (!force && on == monotone_on_ && config_->monotone_penalty == monotone_penalty_) return;
+  monotone_on_ = on;
+  monotone_penalty_ = config_->monotone_penalty;
+  for (Shard& s : shards_) Check(gbl_learner_set_monotone(s.learner, on ? 1 : 0, monotone_penalty_));
 }
 
 void B200TreeLearner::PushFeatureMask() {
@@ -257,6 +268,7 @@ void B200TreeLearner::ResetConfig(const Config* config) {
     });
     InitQuantRandom();
   }
+  PushMonotone(false);
   if (col_sampler_ != nullptr) {
     col_sampler_->SetConfig(config_);  // serial_tree_learner.cpp:168
     PushFeatureMask();

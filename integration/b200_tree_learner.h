@@ -70,6 +70,7 @@ class B200TreeLearner : public TreeLearner {
   void CreateLearners();
   void InitQuantRandom();
   void PushFeatureMask();
+  void PushMonotone(bool force);
   // runs fn(shard) on one host thread per shard (collective C-ABI calls must be issued concurrently)
   template <typename F>
   void ForEachShard(F fn) const;
@@ -87,6 +88,8 @@ class B200TreeLearner : public TreeLearner {
   std::mt19937 quant_start_engine_;
   std::uniform_int_distribution<data_size_t> quant_start_dist_;
   // rows the last tree was trained on (SetBaggingData), and the leaf of every row after the last Train
+  bool monotone_on_ = false;
+  double monotone_penalty_ = 0.0;
   bool bagging_ = false;
   mutable bool leaf_assignment_valid_ = false;
   mutable std::vector<int32_t> leaf_of_row_;

@@ -23,7 +23,7 @@ class GblError(RuntimeError):
 
 class FeatureMeta(ctypes.Structure):
     _fields_ = [("num_bin", ctypes.c_int32), ("missing_type", ctypes.c_int32), ("default_bin", ctypes.c_int32),
-                ("most_freq_bin", ctypes.c_int32), ("real_index", ctypes.c_int32), ("reserved", ctypes.c_int32),
+                ("most_freq_bin", ctypes.c_int32), ("real_index", ctypes.c_int32), ("monotone_type", ctypes.c_int32),
                 ("penalty", ctypes.c_double)]
 
 
@@ -82,7 +82,7 @@ EXPORTED_SYMBOLS = [
     "gbl_dataset_create_from_bins", "gbl_dataset_create_from_mat_f32", "gbl_dataset_free", "gbl_dataset_num_data",
     "gbl_dataset_get_feature_bins", "gbl_dataset_get_feature_bins_rowmajor",
     "gbl_comm_get_unique_id", "gbl_comm_create", "gbl_comm_free", "gbl_comm_allreduce_host_f64", "gbl_comm_info",
-    "gbl_learner_create", "gbl_learner_free", "gbl_learner_reset_config", "gbl_learner_set_feature_mask",
+    "gbl_learner_create", "gbl_learner_free", "gbl_learner_reset_config", "gbl_learner_set_feature_mask", "gbl_learner_set_monotone",
     "gbl_learner_set_bagging_data", "gbl_learner_bagging_dev", "gbl_learner_bagging_balanced_dev", "gbl_learner_bagging_by_query_dev", "gbl_learner_set_quant_random", "gbl_learner_set_quant_random_start",
     "gbl_learner_train", "gbl_learner_train_host", "gbl_learner_train_async", "gbl_learner_train_finish",
     "gbl_learner_add_prediction_to_score", "gbl_learner_add_prediction_to_score_dev",

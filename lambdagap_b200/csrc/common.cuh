@@ -84,6 +84,7 @@ struct FeatMeta {
   int real_index;
   int offset;  // most_freq_bin == 0 (FeatureMetainfo::offset, feature_histogram.hpp:1429-1433)
   int bits;    // 8, or 4 when num_bin <= 16: two rows per byte, even row in the low nibble (dense_bin.hpp:69-82)
+  int monotone_type;  // FeatureMetainfo::monotone_type (-1 / 0 / +1)
   double penalty;
   long long col_off;  // byte offset of this feature's column in Dataset::col_bins
 };
@@ -130,6 +131,7 @@ struct Node {
   long long ig;
   long long ih;
   double output;  // LeafSplits::weight(), parent_output of the children
+  double cmin, cmax;  // monotone constraints (method basic): the interval this leaf's output must stay in
   double bval;    // bottleneck priority: min of best.gain over the path root..node (<= 0 -> never split)
   BestSplit best;
 };
@@ -187,7 +189,8 @@ struct LearnerParams {  // by-value kernel argument
   int num_features;
   int num_tiles;
   int num_ranks;
-  int pad;
+  int use_mc;  // config.monotone_constraints is not empty: the reference's USE_MC path for every feature
+  double monotone_penalty;
   double min_sum_hessian_in_leaf;
   double lambda_l1, lambda_l2, min_gain_to_split, max_delta_step, path_smooth;
 };

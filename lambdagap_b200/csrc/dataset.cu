@@ -132,6 +132,7 @@ static Dataset* alloc_dataset(const gbl_feature_meta* metas, int num_features, i
     m.real_index = metas[f].real_index;
     m.offset = metas[f].most_freq_bin == 0 ? 1 : 0;
     m.penalty = metas[f].penalty;
+    m.monotone_type = metas[f].monotone_type;
     // the reference packs two rows per byte when a feature has at most 16 bins (bin.cpp:615-625 -> DenseBin<.., true>)
     m.bits = metas[f].num_bin <= 16 ? 4 : 8;
     m.col_off = ds->col_bytes;

@@ -44,6 +44,8 @@ struct Learner {
   int* idx[3] = {nullptr, nullptr, nullptr};
   uint8_t* rec = nullptr;  // row records (bins + gradient pair), rebuilt when the gradient format changes
   bool rec_quant = false;
+  bool use_mc = false;            // gbl_learner_set_monotone
+  double monotone_penalty = 0.0;
   short* gh_q = nullptr;
   unsigned short* leaf_u16 = nullptr;  // leaf id per row, scratch of the score update
   long long* hist_pool = nullptr;
@@ -167,6 +169,8 @@ static LearnerParams make_params(const Learner* L) {
   p.num_features = L->ds->num_features;
   p.num_tiles = L->ds->num_tiles;
   p.num_ranks = L->comm != nullptr ? L->comm->num_ranks : 1;
+  p.use_mc = L->use_mc ? 1 : 0;
+  p.monotone_penalty = L->monotone_penalty;
   p.min_sum_hessian_in_leaf = c.min_sum_hessian_in_leaf;
   p.lambda_l1 = c.lambda_l1;
   p.lambda_l2 = c.lambda_l2;
@@ -985,6 +989,20 @@ int gbl_learner_reset_config(gbl_learner* learner, const gbl_learner_config* con
     L->dev.p = make_params(L);
   }
   setup_peer(L);  // collective: the ranks of a data-parallel learner reset their configuration together
+  GBL_API_END();
+}
+
+int gbl_learner_set_monotone(gbl_learner* learner, int32_t enabled, double monotone_penalty) {
+  GBL_API_BEGIN();
+  Learner* L = LEARNER(learner);
+  if (L == nullptr) fatal("gbl_learner_set_monotone: null learner");
+  if (monotone_penalty < 0.0) fatal("gbl_learner_set_monotone: monotone_penalty must be >= 0");
+  DeviceGuard guard(L->ds->device);
+  GBL_CUDA(cudaStreamSynchronize(L->stream));
+  drop_graph(L);  // the kernels take the parameters by value
+  L->use_mc = enabled != 0;
+  L->monotone_penalty = monotone_penalty;
+  L->dev.p = make_params(L);
   GBL_API_END();
 }
 

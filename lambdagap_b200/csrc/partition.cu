@@ -207,6 +207,21 @@ __global__ void __launch_bounds__(kPlanThreads) part_plan_kernel(LearnerDev d) {
     B.ih = bs.right_ih;
     B.output = bs.right_output;
     B.slot = left_smaller ? P.slot : fresh;
+    // BasicLeafConstraints::Update (monotone_constraints.hpp:487-503): both children inherit the leaf's interval; a
+    // split on a constrained feature tightens it at the mid-point of the two outputs (left child = `leaf`, right = new)
+    A.cmin = B.cmin = P.cmin;
+    A.cmax = B.cmax = P.cmax;
+    if (d.p.use_mc) {
+      const int mt = d.meta[bs.feature].monotone_type;
+      const double mid = (bs.left_output + bs.right_output) / 2.0f;
+      if (mt < 0) {
+        A.cmin = fmax(mid, A.cmin);
+        B.cmax = fmin(mid, B.cmax);
+      } else if (mt > 0) {
+        A.cmax = fmin(mid, A.cmax);
+        B.cmin = fmax(mid, B.cmin);
+      }
+    }
     Node* ch[2] = {&A, &B};
     for (int k = 0; k < 2; ++k) {
       Node& X = *ch[k];

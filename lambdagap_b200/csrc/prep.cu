@@ -77,6 +77,8 @@ __global__ void __launch_bounds__(256) tree_begin_kernel(LearnerDev d, int root_
     R.ig = 0;
     R.ih = 0;
     R.output = 0.0;
+    R.cmin = -1.7976931348623157e308;  // BasicConstraint(): [-max double, +max double] (monotone_constraints.hpp:52)
+    R.cmax = 1.7976931348623157e308;
     R.bval = -INFINITY;
     R.best.gain = -INFINITY;  // SplitInfo::Reset (split_info.hpp:132-136)
     R.best.feature = -1;

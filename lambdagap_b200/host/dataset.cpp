@@ -104,7 +104,7 @@ Dataset* Dataset::CreateFromMatWithSample(const void* data, int data_type, int32
     metas[f].default_bin = static_cast<int>(m->GetDefaultBin());
     metas[f].most_freq_bin = static_cast<int>(m->GetMostFreqBin());
     metas[f].real_index = ds->used_feature_map_inv_[f];
-    metas[f].reserved = 0;
+    metas[f].monotone_type = 0;  // monotone constraints are refused by this host layer's Config
     metas[f].penalty = 1.0;
     bounds.insert(bounds.end(), m->bin_upper_bound().begin(), m->bin_upper_bound().end());
   }

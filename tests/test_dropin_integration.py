@@ -70,6 +70,17 @@ CASES = {
                 "verbose=-1 num_threads=4", 1e-5),
     "goss": ("objective=binary num_leaves=31 learning_rate=0.1 data_sample_strategy=goss top_rate=0.2 other_rate=0.1 "
              "verbose=-1 num_threads=4", 1e-5),
+    # monotone constraints, method basic: +1 on column 0, -1 on column 1, +1 on column 4 (20 columns)
+    "monotone_float": ("objective=binary num_leaves=63 learning_rate=0.1 verbose=-1 num_threads=4 "
+                       "monotone_constraints=1,-1,0,0,1,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0", 1e-5),
+    "monotone_quantized_penalty": ("objective=binary num_leaves=63 learning_rate=0.1 verbose=-1 num_threads=4 "
+                                   "use_quantized_grad=true stochastic_rounding=false monotone_penalty=1.5 lambda_l2=1.0 "
+                                   "monotone_constraints=1,-1,0,0,1,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0", 1e-9),
+    # L1 / max_delta_step clip many candidate outputs to the same value, which multiplies exact gain ties between the two
+    # scan directions; quantized gradients make both sides resolve them on identical integer sums
+    "monotone_regression_l1l2": ("objective=regression num_leaves=31 learning_rate=0.1 verbose=-1 num_threads=4 lambda_l1=0.1 "
+                                 "lambda_l2=0.5 max_delta_step=0.8 use_quantized_grad=true stochastic_rounding=false "
+                                 "monotone_constraints=-1,0,1,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0", 1e-9),
     "feature_fraction": ("objective=binary num_leaves=31 learning_rate=0.1 feature_fraction=0.6 feature_fraction_seed=9 "
                          "verbose=-1 num_threads=4", 1e-5),
 }
@@ -79,7 +90,7 @@ CASES = {
 def test_dropin_equals_reference_cpu(gpu, tmp_path, name):
     params, rtol = CASES[name]
     X, y = H.make_binary(120_000, 20, seed=3, nan_frac=0.02, zero_frac=0.2)
-    if name.startswith("regression"):
+    if "regression" in name:
         y = (X[:, 0] * 0.5 + np.nan_to_num(X[:, 2]) + 0.1 * np.random.default_rng(1).normal(size=len(y))).astype(np.float32)
     iters = 4
     ours, s_ours = _run_dropin(tmp_path, X, y, params + " device_type=cuda", iters)
