@@ -60,6 +60,8 @@ typedef struct gbl_feature_meta {
   int32_t real_index;    /* Dataset::RealFeatureIndex(inner): original column, used for split tie-breaks */
   int32_t monotone_type; /* FeatureMetainfo::monotone_type: -1 / 0 / +1 (config.monotone_constraints), 0 by default */
   double penalty;        /* FeatureMetainfo::penalty (feature_contri), 1.0 by default */
+  int32_t bin_type;      /* BinMapper::bin_type(): 0 = numerical, 1 = categorical (include/LightGBM/bin.h:22-25) */
+  int32_t reserved;
 } gbl_feature_meta;
 
 /* The Config fields the hot path reads (include/LightGBM/config.h). */
@@ -103,6 +105,11 @@ typedef struct gbl_split_record {
   double gain;           /* SplitInfo::gain (min_gain_to_split not yet re-added) */
   int64_t left_sum_gradient_and_hessian;  /* quantized mode: packed int32 grad << 32 | uint32 hess */
   int64_t right_sum_gradient_and_hessian;
+  /* categorical split (SplitInfo::cat_threshold, split_info.hpp:45-47) as a bitset over the feature's bins: bin b goes
+   * left iff bit b is set; num_cat_bins = number of set bits, 0 for a numerical split */
+  uint32_t cat_bitset[8];
+  int32_t num_cat_bins;
+  int32_t reserved2;
 } gbl_split_record;
 
 /* Result header of one trained tree. */
@@ -174,6 +181,10 @@ GBL_API int gbl_learner_reset_config(gbl_learner* learner, const gbl_learner_con
  * (gbl_feature_meta.monotone_type).  `monotone_penalty`: config.h:532, applied to the gain of splits on constrained
  * features by depth (monotone_constraints.hpp:357-366).  Call before training; drops the captured tree. */
 GBL_API int gbl_learner_set_monotone(gbl_learner* learner, int32_t enabled, double monotone_penalty);
+/* Categorical split search parameters (config.h:480-501; FindBestThresholdCategoricalInner,
+ * src/treelearner/feature_histogram.cpp:142-380).  Defaults of the reference: 32, 10.0, 10.0, 4, 100. */
+GBL_API int gbl_learner_set_categorical(gbl_learner* learner, int32_t max_cat_threshold, double cat_l2, double cat_smooth,
+                                        int32_t max_cat_to_onehot, int32_t min_data_per_group);
 GBL_API int gbl_learner_set_feature_mask(gbl_learner* learner, const int8_t* is_feature_used_host);
 /* TreeLearner::SetBaggingData (tree_learner.h:75): sorted row subset used for the next trees; NULL/0 = all rows */
 GBL_API int gbl_learner_set_bagging_data(gbl_learner* learner, const int32_t* used_indices_host, int32_t num_used);

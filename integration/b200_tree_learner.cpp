@@ -13,6 +13,7 @@
 
 #include <LightGBM/bin.h>
 #include <LightGBM/objective_function.h>
+#include <LightGBM/utils/common.h>
 #include <LightGBM/utils/log.h>
 #include <LightGBM/utils/openmp_wrapper.h>
 
@@ -117,8 +118,7 @@ void B200TreeLearner::BuildDeviceData() {
   std::vector<gbl_feature_meta> metas(nf);
   for (int f = 0; f < nf; ++f) {
     const BinMapper* m = train_data_->FeatureBinMapper(f);
-    if (m->bin_type() != BinType::NumericalBin)
-      Log::Fatal("B200 tree learner: categorical features are not supported (feature %d)", train_data_->RealFeatureIndex(f));
+    const bool categorical = m->bin_type() == BinType::CategoricalBin;
     if (m->num_bin() > 256) Log::Fatal("B200 tree learner: feature %d has %d bins; at most 256 (max_bin <= 255) are supported",
                                        train_data_->RealFeatureIndex(f), m->num_bin());
     metas[f].num_bin = m->num_bin();
@@ -127,7 +127,10 @@ void B200TreeLearner::BuildDeviceData() {
     metas[f].most_freq_bin = static_cast<int>(m->GetMostFreqBin());
     metas[f].real_index = train_data_->RealFeatureIndex(f);
     // FeatureMetainfo::monotone_type (feature_histogram.hpp:1440-1444): indexed by the ORIGINAL column
-    metas[f].monotone_type = config_->monotone_constraints.empty() ? 0 : static_cast<int>(config_->monotone_constraints[train_data_->RealFeatureIndex(f)]);
+    metas[f].monotone_type = (config_->monotone_constraints.empty() || categorical)
+                                 ? 0
+                                 : static_cast<int>(config_->monotone_constraints[train_data_->RealFeatureIndex(f)]);
+    metas[f].bin_type = categorical ? 1 : 0;
     // feature_contri (FeatureMetainfo::penalty, feature_histogram.hpp:1435-1439)
     const int real = train_data_->RealFeatureIndex(f);
     metas[f].penalty = config_->feature_contri.empty() ? 1.0 : config_->feature_contri[real];
@@ -212,10 +215,22 @@ void B200TreeLearner::InitQuantRandom() {
 // `!monotone_constraints.empty()` selects the reference's USE_MC code path for every feature (feature_histogram.hpp:246-260)
 void B200TreeLearner::PushMonotone(bool force) {
   const bool on = !config_->monotone_constraints.empty();
-  if (!force && on == monotone_on_ && config_->monotone_penalty == monotone_penalty_) return;
+  const bool same_cat = config_->max_cat_threshold == cat_params_[0] && config_->max_cat_to_onehot == cat_params_[1] &&
+                        config_->min_data_per_group == cat_params_[2] && config_->cat_l2 == cat_l2_ && config_->cat_smooth == cat_smooth_;
+  if (!force && on == monotone_on_ && config_->monotone_penalty == monotone_penalty_ && same_cat) return;
+  cat_params_[0] = config_->max_cat_threshold;
+  cat_params_[1] = config_->max_cat_to_onehot;
+  cat_params_[2] = config_->min_data_per_group;
+  cat_l2_ = config_->cat_l2;
+  cat_smooth_ = config_->cat_smooth;
   monotone_on_ = on;
   monotone_penalty_ = config_->monotone_penalty;
-  for (Shard& s : shards_) Check(gbl_learner_set_monotone(s.learner, on ? 1 : 0, monotone_penalty_));
+  for (Shard& s : shards_) {
+    Check(gbl_learner_set_monotone(s.learner, on ? 1 : 0, monotone_penalty_));
+    // categorical split search parameters (config.h:480-501)
+    Check(gbl_learner_set_categorical(s.learner, config_->max_cat_threshold, config_->cat_l2, config_->cat_smooth,
+                                      config_->max_cat_to_onehot, config_->min_data_per_group));
+  }
 }
 
 void B200TreeLearner::PushFeatureMask() {
@@ -300,6 +315,24 @@ Tree* B200TreeLearner::Train(const score_t* gradients, const score_t* hessians, 
   tree->SetLeafOutput(0, s0.result.root_output);  // serial_tree_learner.cpp:205-208
   for (int k = 0; k < s0.result.num_splits; ++k) {
     const gbl_split_record& r = s0.records[k];
+    if (r.num_cat_bins > 0) {
+      // SerialTreeLearner::SplitInner, categorical branch (serial_tree_learner.cpp:811-848): the bins that go left as a
+      // bitset over inner bins, and the same set translated to category values (Dataset::RealThreshold)
+      std::vector<uint32_t> bins;
+      for (uint32_t b = 0; b < 256; ++b) {
+        if ((r.cat_bitset[b >> 5] >> (b & 31)) & 1u) bins.push_back(b);
+      }
+      std::vector<uint32_t> cat_bitset_inner = Common::ConstructBitset(bins.data(), static_cast<int>(bins.size()));
+      std::vector<int> threshold_int(bins.size());
+      for (size_t i = 0; i < bins.size(); ++i) threshold_int[i] = static_cast<int>(train_data_->RealThreshold(r.feature, bins[i]));
+      std::vector<uint32_t> cat_bitset = Common::ConstructBitset(threshold_int.data(), static_cast<int>(threshold_int.size()));
+      tree->SplitCategorical(r.leaf, r.feature, r.real_feature, cat_bitset_inner.data(), static_cast<int>(cat_bitset_inner.size()),
+                             cat_bitset.data(), static_cast<int>(cat_bitset.size()), r.left_output, r.right_output, r.left_count,
+                             r.right_count, r.left_sum_hessian, r.right_sum_hessian,
+                             static_cast<float>(r.gain + config_->min_gain_to_split),
+                             train_data_->FeatureBinMapper(r.feature)->missing_type());
+      continue;
+    }
     // SerialTreeLearner::SplitInner -> Tree::Split (serial_tree_learner.cpp:798-810)
     tree->Split(r.leaf, r.feature, r.real_feature, r.threshold_bin, train_data_->RealThreshold(r.feature, r.threshold_bin),
                 r.left_output, r.right_output, r.left_count, r.right_count, r.left_sum_hessian, r.right_sum_hessian,

@@ -90,6 +90,8 @@ class B200TreeLearner : public TreeLearner {
   // rows the last tree was trained on (SetBaggingData), and the leaf of every row after the last Train
   bool monotone_on_ = false;
   double monotone_penalty_ = 0.0;
+  int cat_params_[3] = {0, 0, 0};
+  double cat_l2_ = -1.0, cat_smooth_ = -1.0;
   bool bagging_ = false;
   mutable bool leaf_assignment_valid_ = false;
   mutable std::vector<int32_t> leaf_of_row_;

@@ -24,7 +24,7 @@ class GblError(RuntimeError):
 class FeatureMeta(ctypes.Structure):
     _fields_ = [("num_bin", ctypes.c_int32), ("missing_type", ctypes.c_int32), ("default_bin", ctypes.c_int32),
                 ("most_freq_bin", ctypes.c_int32), ("real_index", ctypes.c_int32), ("monotone_type", ctypes.c_int32),
-                ("penalty", ctypes.c_double)]
+                ("penalty", ctypes.c_double), ("bin_type", ctypes.c_int32), ("reserved", ctypes.c_int32)]
 
 
 class LearnerConfig(ctypes.Structure):
@@ -43,7 +43,8 @@ class SplitRecord(ctypes.Structure):
                 ("right_output", ctypes.c_double), ("left_sum_gradient", ctypes.c_double),
                 ("left_sum_hessian", ctypes.c_double), ("right_sum_gradient", ctypes.c_double),
                 ("right_sum_hessian", ctypes.c_double), ("gain", ctypes.c_double),
-                ("left_sum_gradient_and_hessian", ctypes.c_int64), ("right_sum_gradient_and_hessian", ctypes.c_int64)]
+                ("left_sum_gradient_and_hessian", ctypes.c_int64), ("right_sum_gradient_and_hessian", ctypes.c_int64),
+                ("cat_bitset", ctypes.c_uint32 * 8), ("num_cat_bins", ctypes.c_int32), ("reserved2", ctypes.c_int32)]
 
 
 class TreeResult(ctypes.Structure):
@@ -82,7 +83,7 @@ EXPORTED_SYMBOLS = [
     "gbl_dataset_create_from_bins", "gbl_dataset_create_from_mat_f32", "gbl_dataset_free", "gbl_dataset_num_data",
     "gbl_dataset_get_feature_bins", "gbl_dataset_get_feature_bins_rowmajor",
     "gbl_comm_get_unique_id", "gbl_comm_create", "gbl_comm_free", "gbl_comm_allreduce_host_f64", "gbl_comm_info",
-    "gbl_learner_create", "gbl_learner_free", "gbl_learner_reset_config", "gbl_learner_set_feature_mask", "gbl_learner_set_monotone",
+    "gbl_learner_create", "gbl_learner_free", "gbl_learner_reset_config", "gbl_learner_set_feature_mask", "gbl_learner_set_monotone", "gbl_learner_set_categorical",
     "gbl_learner_set_bagging_data", "gbl_learner_bagging_dev", "gbl_learner_bagging_balanced_dev", "gbl_learner_bagging_by_query_dev", "gbl_learner_set_quant_random", "gbl_learner_set_quant_random_start",
     "gbl_learner_train", "gbl_learner_train_host", "gbl_learner_train_async", "gbl_learner_train_finish",
     "gbl_learner_add_prediction_to_score", "gbl_learner_add_prediction_to_score_dev",
@@ -333,7 +334,9 @@ class Learner:
         recs = []
         for k in range(n):
             r = self._records[k]
-            recs.append({name: getattr(r, name) for name, _ in SplitRecord._fields_})
+            rec = {name: getattr(r, name) for name, _ in SplitRecord._fields_}
+            rec["cat_bitset"] = tuple(int(w) for w in r.cat_bitset)  # a plain value: records compare with ==
+            recs.append(rec)
         res = {name: getattr(self._result, name) for name, _ in TreeResult._fields_}
         return res, recs
 

@@ -85,6 +85,7 @@ struct FeatMeta {
   int offset;  // most_freq_bin == 0 (FeatureMetainfo::offset, feature_histogram.hpp:1429-1433)
   int bits;    // 8, or 4 when num_bin <= 16: two rows per byte, even row in the low nibble (dense_bin.hpp:69-82)
   int monotone_type;  // FeatureMetainfo::monotone_type (-1 / 0 / +1)
+  int is_categorical; // BinMapper::bin_type() == CategoricalBin
   double penalty;
   long long col_off;  // byte offset of this feature's column in Dataset::col_bins
 };
@@ -108,6 +109,10 @@ struct BestSplit {
   long long left_ih;
   long long right_ig;
   long long right_ih;
+  // categorical split: bins that go left (SplitInfo::cat_threshold as a bitset over mapper bins); num_cat == 0: numerical
+  unsigned cat_bits[8];
+  int num_cat;
+  int pad;
 };
 
 // One node of the tree under construction.  LeafSplits (src/treelearner/leaf_splits.hpp:22-275) + the
@@ -191,6 +196,9 @@ struct LearnerParams {  // by-value kernel argument
   int num_ranks;
   int use_mc;  // config.monotone_constraints is not empty: the reference's USE_MC path for every feature
   double monotone_penalty;
+  // categorical split search (config.h:480-501)
+  int max_cat_threshold, max_cat_to_onehot, min_data_per_group, pad_cat;
+  double cat_l2, cat_smooth;
   double min_sum_hessian_in_leaf;
   double lambda_l1, lambda_l2, min_gain_to_split, max_delta_step, path_smooth;
 };

@@ -133,6 +133,7 @@ static Dataset* alloc_dataset(const gbl_feature_meta* metas, int num_features, i
     m.offset = metas[f].most_freq_bin == 0 ? 1 : 0;
     m.penalty = metas[f].penalty;
     m.monotone_type = metas[f].monotone_type;
+    m.is_categorical = metas[f].bin_type == 1 ? 1 : 0;
     // the reference packs two rows per byte when a feature has at most 16 bins (bin.cpp:615-625 -> DenseBin<.., true>)
     m.bits = metas[f].num_bin <= 16 ? 4 : 8;
     m.col_off = ds->col_bytes;

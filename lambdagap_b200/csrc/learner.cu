@@ -46,6 +46,8 @@ struct Learner {
   bool rec_quant = false;
   bool use_mc = false;            // gbl_learner_set_monotone
   double monotone_penalty = 0.0;
+  int max_cat_threshold = 32, max_cat_to_onehot = 4, min_data_per_group = 100;  // gbl_learner_set_categorical
+  double cat_l2 = 10.0, cat_smooth = 10.0;
   short* gh_q = nullptr;
   unsigned short* leaf_u16 = nullptr;  // leaf id per row, scratch of the score update
   long long* hist_pool = nullptr;
@@ -171,6 +173,11 @@ static LearnerParams make_params(const Learner* L) {
   p.num_ranks = L->comm != nullptr ? L->comm->num_ranks : 1;
   p.use_mc = L->use_mc ? 1 : 0;
   p.monotone_penalty = L->monotone_penalty;
+  p.max_cat_threshold = L->max_cat_threshold;
+  p.max_cat_to_onehot = L->max_cat_to_onehot;
+  p.min_data_per_group = L->min_data_per_group;
+  p.cat_l2 = L->cat_l2;
+  p.cat_smooth = L->cat_smooth;
   p.min_sum_hessian_in_leaf = c.min_sum_hessian_in_leaf;
   p.lambda_l1 = c.lambda_l1;
   p.lambda_l2 = c.lambda_l2;
@@ -1002,6 +1009,25 @@ int gbl_learner_set_monotone(gbl_learner* learner, int32_t enabled, double monot
   drop_graph(L);  // the kernels take the parameters by value
   L->use_mc = enabled != 0;
   L->monotone_penalty = monotone_penalty;
+  L->dev.p = make_params(L);
+  GBL_API_END();
+}
+
+int gbl_learner_set_categorical(gbl_learner* learner, int32_t max_cat_threshold, double cat_l2, double cat_smooth,
+                                int32_t max_cat_to_onehot, int32_t min_data_per_group) {
+  GBL_API_BEGIN();
+  Learner* L = LEARNER(learner);
+  if (L == nullptr) fatal("gbl_learner_set_categorical: null learner");
+  if (max_cat_threshold <= 0) fatal("gbl_learner_set_categorical: max_cat_threshold must be > 0");
+  if (cat_l2 < 0.0 || cat_smooth < 0.0) fatal("gbl_learner_set_categorical: cat_l2 / cat_smooth must be >= 0");
+  DeviceGuard guard(L->ds->device);
+  GBL_CUDA(cudaStreamSynchronize(L->stream));
+  drop_graph(L);
+  L->max_cat_threshold = max_cat_threshold;
+  L->cat_l2 = cat_l2;
+  L->cat_smooth = cat_smooth;
+  L->max_cat_to_onehot = max_cat_to_onehot;
+  L->min_data_per_group = min_data_per_group;
   L->dev.p = make_params(L);
   GBL_API_END();
 }

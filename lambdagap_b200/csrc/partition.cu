@@ -35,6 +35,8 @@ struct SplitRule {
   int threshold;
   int missing_bin;  // -1 = none
   bool default_left;
+  const unsigned* cat;  // categorical split: bitset of the bins that go left (DenseBin::SplitCategoricalInner,
+                        // dense_bin.hpp:450-483: in mapper-bin terms "left iff the bin is in the set"), else nullptr
 };
 
 __device__ inline SplitRule load_rule(const LearnerDev& d, const BestSplit& bs) {
@@ -47,11 +49,13 @@ __device__ inline SplitRule load_rule(const LearnerDev& d, const BestSplit& bs) 
   if (m.missing_type == GBL_MISSING_ZERO) r.missing_bin = m.default_bin;
   if (m.missing_type == GBL_MISSING_NAN) r.missing_bin = m.num_bin - 1;
   r.default_left = bs.default_left != 0;
+  r.cat = bs.num_cat > 0 ? bs.cat_bits : nullptr;
   return r;
 }
 
 __device__ inline bool goes_left(const SplitRule& r, int row) {
   const int bin = r.bits == 4 ? ((__ldg(r.col + (row >> 1)) >> ((row & 1) << 2)) & 0xf) : __ldg(r.col + row);
+  if (r.cat != nullptr) return (__ldg(r.cat + (bin >> 5)) >> (bin & 31)) & 1u;
   return bin == r.missing_bin ? r.default_left : bin <= r.threshold;
 }
 
@@ -105,7 +109,12 @@ __global__ void __launch_bounds__(kPartThreads) part_count_kernel(LearnerDev d) 
     int cnt = 0;
 #pragma unroll
     for (int k = 0; k < kIters; ++k) {
-      const bool left = bins[k] >= 0 && (bins[k] == rule.missing_bin ? rule.default_left : bins[k] <= rule.threshold);
+      bool left;
+      if (rule.cat != nullptr) {  // CTA-uniform
+        left = bins[k] >= 0 && ((__ldg(rule.cat + (bins[k] >> 5)) >> (bins[k] & 31)) & 1u) != 0u;
+      } else {
+        left = bins[k] >= 0 && (bins[k] == rule.missing_bin ? rule.default_left : bins[k] <= rule.threshold);
+      }
       const unsigned bl = __ballot_sync(0xffffffffu, left);
       if (lane == 0 && c_begin + k * kPartThreads + warp * 32 < c_end) {
         bits[k * kPartWarps + warp] = bl;
@@ -470,7 +479,8 @@ __global__ void __launch_bounds__(256) add_score_rows_kernel(LearnerDev d, const
       int missing_bin = -1;
       if (m.missing_type == GBL_MISSING_ZERO) missing_bin = m.default_bin;
       if (m.missing_type == GBL_MISSING_NAN) missing_bin = m.num_bin - 1;
-      const bool left = bin == missing_bin ? nd.best.default_left != 0 : bin <= static_cast<int>(nd.best.threshold);
+      bool left = bin == missing_bin ? nd.best.default_left != 0 : bin <= static_cast<int>(nd.best.threshold);
+      if (nd.best.num_cat > 0) left = ((nd.best.cat_bits[bin >> 5] >> (bin & 31)) & 1u) != 0u;  // Tree::CategoricalDecisionInner
       n = nd.left + (left ? 0 : 1);
     }
     score[row] += scale * leaf_values[d.nodes[n].ref_leaf] + bias;

@@ -145,3 +145,39 @@ def test_dropin_refuses_what_the_learner_does_not_implement(gpu, tmp_path):
     r = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "dropin_runner.py"), src, dst], capture_output=True, text=True,
                        timeout=300)
     assert r.returncode != 0 and "extra_trees is not supported" in (r.stdout + r.stderr)
+
+
+@pytest.mark.parametrize("mode", ["float", "quantized", "small_groups"])
+def test_dropin_categorical(gpu, tmp_path, mode):
+    """Categorical splits (FindBestThresholdCategoricalInner / ...IntInner, feature_histogram.cpp:142-700): one-vs-rest for a
+    3-category column (num_bin <= max_cat_to_onehot), the sorted many-vs-many search for 40- and 200-category columns, next
+    to numerical columns.  The split's bin set travels as a bitset; Tree::SplitCategorical writes it into the model."""
+    rng = np.random.default_rng(21)
+    n = 150_000
+    X = rng.normal(size=(n, 10)).astype(np.float32)
+    c0 = rng.integers(0, 3, size=n)
+    c1 = rng.integers(0, 40, size=n)
+    c2 = (rng.zipf(1.3, size=n) % 200)
+    e1 = rng.normal(size=40)
+    e2 = rng.normal(size=200)
+    X[:, 0], X[:, 1], X[:, 2] = c0, c1, c2
+    logit = 0.8 * (c0 == 1) + e1[c1] + 0.7 * e2[c2] + X[:, 3] - 0.5 * X[:, 4] + 0.5 * rng.normal(size=n)
+    y = (logit > np.median(logit)).astype(np.float32)
+    dsp = "max_bin=255 verbose=-1 categorical_feature=0,1,2"
+    params = "objective=binary num_leaves=63 learning_rate=0.1 verbose=-1 num_threads=4 " + dsp
+    rtol = 1e-5
+    if mode == "quantized":
+        params += " use_quantized_grad=true stochastic_rounding=false"
+        rtol = 1e-9
+    if mode == "small_groups":
+        params += " min_data_per_group=20 cat_smooth=2 cat_l2=1 max_cat_threshold=16 min_data_in_leaf=10"
+    ours, s_ours = _run_dropin(tmp_path, X, y, params + " device_type=cuda", 4, dataset_params=dsp)
+    ref, s_ref = _run_reference(X, y, params, 4, dataset_params=dsp)
+    assert "cat_threshold" in ref and "num_cat=0" not in ref.split("Tree=0")[1].split("Tree=1")[0], "the case must contain categorical splits"
+    ot, rt = R.parse_model_trees(ours), R.parse_model_trees(ref)
+    _assert_models(ours, ref, rtol)
+    # the categorical thresholds themselves: the cat_boundaries / cat_threshold lines of every tree
+    def cat_lines(text):
+        return [ln for ln in text.split("\n") if ln.startswith(("cat_boundaries=", "cat_threshold=", "num_cat="))]
+    assert cat_lines(ours) == cat_lines(ref)
+    np.testing.assert_allclose(s_ours, s_ref, rtol=max(rtol, 1e-7), atol=1e-9)
