@@ -197,7 +197,7 @@ struct LearnerParams {  // by-value kernel argument
   int use_mc;  // config.monotone_constraints is not empty: the reference's USE_MC path for every feature
   double monotone_penalty;
   // categorical split search (config.h:480-501)
-  int max_cat_threshold, max_cat_to_onehot, min_data_per_group, pad_cat;
+  int max_cat_threshold, max_cat_to_onehot, min_data_per_group, num_cat_features;
   double cat_l2, cat_smooth;
   double min_sum_hessian_in_leaf;
   double lambda_l1, lambda_l2, min_gain_to_split, max_delta_step, path_smooth;

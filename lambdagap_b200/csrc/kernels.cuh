@@ -29,6 +29,7 @@ struct LearnerDev {
   int gh_off;              // byte offset of the gradient pair inside a tile block
   int num_data;  // local rows
   const FeatMeta* meta;
+  const int* cat_features;  // [p.num_cat_features] inner indices of the categorical features (nullptr when there are none)
   // per-tree state
   TreeState* ts;
   Node* nodes;             // [max_nodes]

@@ -48,6 +48,8 @@ struct Learner {
   double monotone_penalty = 0.0;
   int max_cat_threshold = 32, max_cat_to_onehot = 4, min_data_per_group = 100;  // gbl_learner_set_categorical
   double cat_l2 = 10.0, cat_smooth = 10.0;
+  int* cat_features = nullptr;  // device list of the categorical features
+  int num_cat_features = 0;
   short* gh_q = nullptr;
   unsigned short* leaf_u16 = nullptr;  // leaf id per row, scratch of the score update
   long long* hist_pool = nullptr;
@@ -178,6 +180,7 @@ static LearnerParams make_params(const Learner* L) {
   p.min_data_per_group = L->min_data_per_group;
   p.cat_l2 = L->cat_l2;
   p.cat_smooth = L->cat_smooth;
+  p.num_cat_features = L->num_cat_features;
   p.min_sum_hessian_in_leaf = c.min_sum_hessian_in_leaf;
   p.lambda_l1 = c.lambda_l1;
   p.lambda_l2 = c.lambda_l2;
@@ -391,6 +394,18 @@ static Learner* learner_create(const Dataset* ds, const gbl_learner_config* cfg,
   d.col_bins = ds->col_bins;
   d.num_data = static_cast<int>(ds->num_data);
   d.meta = ds->meta_dev;
+  {
+    std::vector<int> cats;
+    for (int f = 0; f < ds->num_features; ++f) {
+      if (ds->meta_host[f].is_categorical) cats.push_back(f);
+    }
+    L->num_cat_features = static_cast<int>(cats.size());
+    if (!cats.empty()) {
+      GBL_CUDA(cudaMalloc(&L->cat_features, sizeof(int) * cats.size()));
+      GBL_CUDA(cudaMemcpy(L->cat_features, cats.data(), sizeof(int) * cats.size(), cudaMemcpyHostToDevice));
+    }
+    d.cat_features = L->cat_features;
+  }
   d.ts = L->ts;
   d.idx[0] = L->idx[0];
   d.idx[1] = L->idx[1];
@@ -422,6 +437,7 @@ static void learner_free(Learner* L) {
   cudaFree(L->gh_q);
   cudaFree(L->leaf_u16);
   cudaFree(L->feature_mask);
+  cudaFree(L->cat_features);
   cudaFree(L->rand_g);
   cudaFree(L->rand_h);
   cudaFree(L->bag_indices);
