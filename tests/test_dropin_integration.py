@@ -181,3 +181,25 @@ def test_dropin_categorical(gpu, tmp_path, mode):
         return [ln for ln in text.split("\n") if ln.startswith(("cat_boundaries=", "cat_threshold=", "num_cat="))]
     assert cat_lines(ours) == cat_lines(ref)
     np.testing.assert_allclose(s_ours, s_ref, rtol=max(rtol, 1e-7), atol=1e-9)
+
+
+def test_dropin_num_gpu_with_categorical_and_monotone(gpu, tmp_path):
+    """Route B with the round-2 split types: two GPUs inside one Booster, a categorical column and monotone constraints,
+    quantized gradients (integer histogram sums make the sharded result equal the CPU's bit for bit)."""
+    if capi.device_count() < 2:
+        pytest.skip("needs two GPUs (run with gpurun --gpus 2)")
+    rng = np.random.default_rng(8)
+    n = 160_000
+    X = rng.normal(size=(n, 8)).astype(np.float32)
+    c = rng.integers(0, 30, size=n)
+    X[:, 0] = c
+    e = rng.normal(size=30)
+    logit = e[c] + X[:, 1] - 0.7 * X[:, 2] + 0.4 * rng.normal(size=n)
+    y = (logit > np.median(logit)).astype(np.float32)
+    dsp = "max_bin=255 verbose=-1 categorical_feature=0"
+    params = ("objective=binary num_leaves=63 learning_rate=0.1 verbose=-1 num_threads=4 use_quantized_grad=true "
+              "stochastic_rounding=false monotone_constraints=0,1,-1,0,0,0,0,0 " + dsp)
+    ours, s_ours = _run_dropin(tmp_path, X, y, params + " device_type=cuda num_gpu=2", 4, dataset_params=dsp)
+    ref, s_ref = _run_reference(X, y, params, 4, dataset_params=dsp)
+    _assert_models(ours, ref, 1e-9)
+    np.testing.assert_allclose(s_ours, s_ref, rtol=1e-7, atol=1e-9)
