@@ -550,6 +550,27 @@ def shape_leg(ctx, which, steps, warmup):
     return out
 
 
+def _json_leg(cmd, timeout_s):
+    try:
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout_s)
+        for line in reversed(r.stdout.strip().split("\n")):
+            if line.startswith("{"):
+                return json.loads(line)
+        return {"error": ("rc=%d " % r.returncode) + (r.stderr or r.stdout)[-300:]}
+    except subprocess.TimeoutExpired:
+        return {"error": "timed out after %d s" % timeout_s}
+    except Exception as ex:
+        return {"error": str(ex)[:300]}
+
+
+def dropin_leg(rows, timeout_s=240):
+    """The reference library with the B200 learner compiled in behind its TreeLearner interface (integration/_ref): the
+    reference's own GBDT on the host (gradients, scores), device_type=cuda -> B200TreeLearner.  Own process."""
+    if not os.path.exists(os.path.join(ROOT, "integration", "_ref", "lib_lightgbm.so")):
+        return {"unavailable": "integration/_ref/lib_lightgbm.so not built (integration/Makefile needs /root/reference)"}
+    return _json_leg([sys.executable, os.path.join(ROOT, "scripts", "dropin_speed.py"), str(rows)], timeout_s)
+
+
 def reference_cuda_leg(rows, timeout_s=240):
     script = os.path.join(ROOT, "scripts", "ref_cuda_leg.py")
     if not os.path.exists(os.path.join(ROOT, "oracle", "_ref_cuda", "lib_lightgbm.so")):
@@ -778,6 +799,9 @@ def main():
     ref_cuda = None
     if rank == 0 and world == 1 and secondary and not args.quantized:
         ref_cuda = reference_cuda_leg(cfg["rows"])
+    dropin = None
+    if rank == 0 and world == 1 and secondary and not args.quantized:
+        dropin = dropin_leg(cfg["rows"])
 
     parity = None
     reg = None
@@ -814,7 +838,7 @@ def main():
                             "expansions_per_tree": prof["expansions"] / max(1, prof["trees"]),
                             "splits_per_tree": prof["splits"] / max(1, prof["trees"])},
                "quantized_mode": quant_leg, "parity": parity, "reg100m": reg, "other_shapes": shapes,
-               "reference_cuda": ref_cuda}
+               "reference_cuda": ref_cuda, "dropin": dropin}
         print(json.dumps(out), flush=True)
     if world > 1:
         dist.barrier()

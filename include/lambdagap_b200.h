@@ -253,6 +253,10 @@ GBL_API int gbl_learner_add_prediction_to_dataset_dev(gbl_learner* learner, cons
  * (src/treelearner/gradient_discretizer.cpp:209-260), which the split records do not carry */
 GBL_API int gbl_learner_get_leaf_values(gbl_learner* learner, double* out_host, int32_t num_leaves);
 GBL_API int gbl_learner_get_leaf_assignment(gbl_learner* learner, int32_t* out_host);
+/* The same as 2-byte leaf ids (trees of at most 65535 leaves; 0xFFFF = row outside the tree's rows), written by the
+ * kernel the device-resident score update uses -- a quarter of the bytes for a host that keeps the scores itself
+ * (SerialTreeLearner::AddPredictionToScore on a host ScoreUpdater, serial_tree_learner.h:100-115). */
+GBL_API int gbl_learner_get_leaf_assignment_u16(gbl_learner* learner, uint16_t* out_host);
 /* index segment of one leaf, in partition order (DataPartition::GetIndexOnLeaf) */
 GBL_API int gbl_learner_get_leaf_indices(gbl_learner* learner, int32_t leaf, int32_t* out_host, int32_t* out_count);
 /* histogram of `leaf`'s slot for `feature` as (gradient, hessian) pairs per mapper bin [num_bin][2]:
@@ -377,6 +381,11 @@ GBL_API int gbl_metric_eval(gbl_metric* metric, const double* score_dev, void* s
  * src/boosting/cuda/cuda_score_updater.cpp:12-80) */
 GBL_API int gbl_device_malloc(int32_t device_id, size_t bytes, void** out_dev);
 GBL_API int gbl_device_free(int32_t device_id, void* ptr_dev);
+/* Page-lock a host buffer the caller keeps passing to this library (the reference's gradient / hessian vectors, which
+ * GBDT allocates once, src/boosting/gbdt.cpp:849-865): copies from pageable memory are staged and run at a fifth of the
+ * PCIe rate.  Failure is reported but harmless (the copies then take the slow path). */
+GBL_API int gbl_host_register(void* ptr_host, size_t bytes);
+GBL_API int gbl_host_unregister(void* ptr_host);
 GBL_API int gbl_memcpy_h2d(int32_t device_id, void* dst_dev, const void* src_host, size_t bytes);
 GBL_API int gbl_memcpy_d2h(int32_t device_id, void* dst_host, const void* src_dev, size_t bytes);
 GBL_API int gbl_device_fill_f64(int32_t device_id, double* dst_dev, double value, int64_t n);

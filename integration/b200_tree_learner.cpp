@@ -36,6 +36,10 @@ B200TreeLearner::B200TreeLearner(const Config* config, int num_gpu) : config_(co
 B200TreeLearner::~B200TreeLearner() { Release(); }
 
 void B200TreeLearner::Release() {
+  for (const score_t* p : registered_) gbl_host_unregister(const_cast<score_t*>(p));
+  registered_.clear();
+  if (!leaf16_.empty()) gbl_host_unregister(leaf16_.data());
+  leaf16_.clear();
   for (Shard& s : shards_) {
     if (s.learner != nullptr) gbl_learner_free(s.learner);
     s.learner = nullptr;
@@ -301,6 +305,12 @@ Tree* B200TreeLearner::Train(const score_t* gradients, const score_t* hessians, 
   if (config_->feature_fraction < 1.0) PushFeatureMask();
   int32_t quant_start = 0;
   if (quant_random_ready_) quant_start = quant_start_dist_(quant_start_engine_);  // gradient_discretizer.cpp:116
+  // GBDT keeps its gradient / hessian vectors for the whole training (gbdt.cpp:849-865): page-lock them the first time
+  // they are seen so that the per-tree upload runs at the PCIe rate instead of through a staging buffer
+  for (const score_t* p : {gradients, hessians}) {
+    if (registered_.insert(p).second && registered_.size() <= 256)
+      gbl_host_register(const_cast<score_t*>(p), sizeof(score_t) * static_cast<size_t>(num_data_));
+  }
   ForEachShard([&](Shard& s) {
     // one GPU: the reference's own offset; shards rotate inside their slice (see the warning in InitQuantRandom)
     const int32_t start = shards_.size() == 1 ? quant_start : quant_start % std::max<data_size_t>(1, s.count);
@@ -382,10 +392,22 @@ void B200TreeLearner::SetBaggingData(const Dataset* /*subset*/, const data_size_
 
 void B200TreeLearner::FetchLeafAssignment() const {
   if (leaf_assignment_valid_) return;
-  leaf_of_row_.resize(num_data_);
-  ForEachShard([&](Shard& s) {
-    if (gbl_learner_get_leaf_assignment(s.learner, leaf_of_row_.data() + s.begin) != 0) throw std::runtime_error(gbl_last_error());
-  });
+  if (config_->num_leaves <= 65535) {
+    // 2-byte leaf ids into a page-locked buffer: a quarter of the bytes of the int32 form at the full PCIe rate
+    if (leaf16_.size() != static_cast<size_t>(num_data_)) {
+      if (!leaf16_.empty()) gbl_host_unregister(leaf16_.data());
+      leaf16_.assign(num_data_, 0xFFFF);
+      gbl_host_register(leaf16_.data(), sizeof(uint16_t) * leaf16_.size());  // failure = slower copies, nothing else
+    }
+    ForEachShard([&](Shard& s) {
+      if (gbl_learner_get_leaf_assignment_u16(s.learner, leaf16_.data() + s.begin) != 0) throw std::runtime_error(gbl_last_error());
+    });
+  } else {
+    leaf_of_row_.resize(num_data_);
+    ForEachShard([&](Shard& s) {
+      if (gbl_learner_get_leaf_assignment(s.learner, leaf_of_row_.data() + s.begin) != 0) throw std::runtime_error(gbl_last_error());
+    });
+  }
   leaf_assignment_valid_ = true;
 }
 
@@ -394,6 +416,14 @@ void B200TreeLearner::AddPredictionToScore(const Tree* tree, double* out_score) 
   // out_score is the host ScoreUpdater's array in this build: leaf of every trained row from the device partition,
   // then score[row] += leaf_output (rows outside the bag carry -1; GBDT::UpdateScore walks the tree for them itself)
   FetchLeafAssignment();
+  if (config_->num_leaves <= 65535) {
+    const uint16_t* leaf = leaf16_.data();
+#pragma omp parallel for num_threads(OMP_NUM_THREADS()) schedule(static)
+    for (data_size_t i = 0; i < num_data_; ++i) {
+      if (leaf[i] != 0xFFFF) out_score[i] += tree->LeafOutput(leaf[i]);
+    }
+    return;
+  }
   const int32_t* leaf = leaf_of_row_.data();
 #pragma omp parallel for num_threads(OMP_NUM_THREADS()) schedule(static)
   for (data_size_t i = 0; i < num_data_; ++i) {
@@ -408,6 +438,10 @@ void B200TreeLearner::RenewTreeOutput(Tree* tree, const ObjectiveFunction* obj,
   // SerialTreeLearner::RenewTreeOutput (serial_tree_learner.cpp:924-966): per leaf, the rows of the leaf
   FetchLeafAssignment();
   const int nl = tree->num_leaves();
+  if (config_->num_leaves <= 65535) {  // one representation below: widen the 2-byte ids
+    leaf_of_row_.resize(num_data_);
+    for (data_size_t i = 0; i < num_data_; ++i) leaf_of_row_[i] = leaf16_[i] == 0xFFFF ? -1 : static_cast<int32_t>(leaf16_[i]);
+  }
   std::vector<data_size_t> begin(nl + 1, 0);
   for (data_size_t i = 0; i < num_data_; ++i) {
     if (leaf_of_row_[i] >= 0 && leaf_of_row_[i] < nl) ++begin[leaf_of_row_[i] + 1];

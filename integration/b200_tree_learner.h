@@ -24,6 +24,7 @@
 
 #include <memory>
 #include <random>
+#include <set>
 #include <vector>
 
 #include "col_sampler.hpp"  // the reference's own ColSampler (src/treelearner/col_sampler.hpp)
@@ -95,6 +96,8 @@ class B200TreeLearner : public TreeLearner {
   bool bagging_ = false;
   mutable bool leaf_assignment_valid_ = false;
   mutable std::vector<int32_t> leaf_of_row_;
+  mutable std::vector<uint16_t> leaf16_;   // page-locked 2-byte leaf ids (trees of at most 65535 leaves)
+  std::set<const score_t*> registered_;    // gradient / hessian buffers of GBDT that have been page-locked
 };
 
 }  // namespace LightGBM

@@ -87,14 +87,14 @@ EXPORTED_SYMBOLS = [
     "gbl_learner_set_bagging_data", "gbl_learner_bagging_dev", "gbl_learner_bagging_balanced_dev", "gbl_learner_bagging_by_query_dev", "gbl_learner_set_quant_random", "gbl_learner_set_quant_random_start",
     "gbl_learner_train", "gbl_learner_train_host", "gbl_learner_train_async", "gbl_learner_train_finish",
     "gbl_learner_add_prediction_to_score", "gbl_learner_add_prediction_to_score_dev",
-    "gbl_learner_add_prediction_out_of_bag_dev", "gbl_learner_add_prediction_to_dataset_dev", "gbl_learner_get_leaf_values", "gbl_learner_get_leaf_assignment", "gbl_learner_get_leaf_indices", "gbl_learner_get_histogram",
+    "gbl_learner_add_prediction_out_of_bag_dev", "gbl_learner_add_prediction_to_dataset_dev", "gbl_learner_get_leaf_values", "gbl_learner_get_leaf_assignment", "gbl_learner_get_leaf_assignment_u16", "gbl_learner_get_leaf_indices", "gbl_learner_get_histogram",
     "gbl_learner_get_discretized", "gbl_learner_histogram_words", "gbl_learner_construct_histogram",
     "gbl_learner_stream", "gbl_learner_set_profiling", "gbl_learner_get_profile", "gbl_learner_timer_record",
     "gbl_learner_timer_elapsed_ms",
     "gbl_objective_create", "gbl_objective_free", "gbl_objective_get_gradients", "gbl_objective_boost_from_score",
     "gbl_objective_is_constant_hessian", "gbl_objective_set_label_counts",
     "gbl_metric_create", "gbl_metric_free", "gbl_metric_num_outputs", "gbl_metric_eval",
-    "gbl_device_malloc", "gbl_device_free", "gbl_memcpy_h2d", "gbl_memcpy_d2h", "gbl_device_fill_f64",
+    "gbl_device_malloc", "gbl_device_free", "gbl_host_register", "gbl_host_unregister", "gbl_memcpy_h2d", "gbl_memcpy_d2h", "gbl_device_fill_f64",
     "gbl_device_synchronize", "gbl_partition_rows_noalloc",
 ]
 

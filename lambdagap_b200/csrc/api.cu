@@ -85,6 +85,25 @@ int gbl_device_free(int32_t device_id, void* ptr_dev) {
   GBL_API_END();
 }
 
+int gbl_host_register(void* ptr_host, size_t bytes) {
+  GBL_API_BEGIN();
+  if (ptr_host == nullptr || bytes == 0) fatal("gbl_host_register: null argument");
+  const cudaError_t e = cudaHostRegister(ptr_host, bytes, cudaHostRegisterPortable);
+  if (e == cudaErrorHostMemoryAlreadyRegistered) {
+    cudaGetLastError();
+  } else if (e != cudaSuccess) {
+    cudaGetLastError();
+    fatal("gbl_host_register: %s", cudaGetErrorString(e));
+  }
+  GBL_API_END();
+}
+
+int gbl_host_unregister(void* ptr_host) {
+  GBL_API_BEGIN();
+  if (ptr_host != nullptr && cudaHostUnregister(ptr_host) != cudaSuccess) cudaGetLastError();
+  GBL_API_END();
+}
+
 int gbl_memcpy_h2d(int32_t device_id, void* dst_dev, const void* src_host, size_t bytes) {
   GBL_API_BEGIN();
   DeviceGuard guard(device_id);

@@ -144,6 +144,7 @@ void launch_partition(const LearnerDev& d, cudaStream_t s);
 void launch_add_score(const LearnerDev& d, const double* leaf_values_dev, double scale, double bias, double* score,
                       unsigned short* leaf_scratch, bool partial_rows, cudaStream_t s);
 void launch_leaf_assignment(const LearnerDev& d, int* out, cudaStream_t s);
+void launch_leaf_mark(const LearnerDev& d, unsigned short* out, bool partial_rows, cudaStream_t s);  // 0xFFFF = not in the tree
 void launch_add_score_rows(const LearnerDev& d, const uint8_t* row_bins, int row_stride, const int* rows, int num_rows,
                            const double* leaf_values_dev, double scale, double bias, double* score, cudaStream_t s);
 

@@ -1390,6 +1390,20 @@ static void download_nodes(Learner* L, std::vector<Node>* nodes, TreeState* ts) 
   GBL_CUDA(cudaMemcpy(nodes->data(), L->nodes, sizeof(Node) * ts->num_nodes, cudaMemcpyDeviceToHost));
 }
 
+int gbl_learner_get_leaf_assignment_u16(gbl_learner* learner, uint16_t* out_host) {
+  GBL_API_BEGIN();
+  Learner* L = LEARNER(learner);
+  if (L == nullptr || out_host == nullptr) fatal("gbl_learner_get_leaf_assignment_u16: null argument");
+  if (!L->has_tree) fatal("gbl_learner_get_leaf_assignment_u16: no tree trained yet");
+  if (L->cfg.num_leaves > 65535) fatal("gbl_learner_get_leaf_assignment_u16: num_leaves=%d does not fit 16 bits", L->cfg.num_leaves);
+  DeviceGuard guard(L->ds->device);
+  const size_t n = static_cast<size_t>(L->ds->num_data);
+  launch_leaf_mark(L->dev, L->leaf_u16, L->bag_indices != nullptr, L->stream);
+  GBL_CUDA(cudaMemcpyAsync(out_host, L->leaf_u16, sizeof(unsigned short) * n, cudaMemcpyDeviceToHost, L->stream));
+  GBL_CUDA(cudaStreamSynchronize(L->stream));
+  GBL_API_END();
+}
+
 int gbl_learner_get_leaf_indices(gbl_learner* learner, int32_t leaf, int32_t* out_host, int32_t* out_count) {
   GBL_API_BEGIN();
   Learner* L = LEARNER(learner);

@@ -514,6 +514,11 @@ void launch_add_score(const LearnerDev& d, const double* leaf_values_dev, double
              score, d.num_data);
 }
 
+void launch_leaf_mark(const LearnerDev& d, unsigned short* out, bool partial_rows, cudaStream_t s) {
+  if (partial_rows) GBL_CUDA(cudaMemsetAsync(out, 0xFF, sizeof(unsigned short) * d.num_data, s));
+  GBL_LAUNCH(leaf_mark_kernel, kPartGrid, 256, 0, s, d, out);
+}
+
 void launch_leaf_assignment(const LearnerDev& d, int* out, cudaStream_t s) {
   GBL_LAUNCH(leaf_assign_kernel, kPartGrid, 256, 0, s, d, out);
 }
