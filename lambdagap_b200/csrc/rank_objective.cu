@@ -17,6 +17,7 @@
 // with the reference's formulas (libm exp / log2) and uploaded once, so table look-ups are bit-identical.
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <vector>
 
 #include "objective.cuh"
@@ -115,19 +116,18 @@ __device__ inline void j_range(int t, int i, int k, int cnt, int* start, int* en
   }
 }
 
-// One pair (ranks i < j) seen from the document at rank `me` (== i or j).  Accumulates into (lam, hes) exactly
-// what the reference adds to that document (rank_objective.hpp:353-513); returns -2 * p_lambda (0 if skipped).
+// p_lambda / p_hessian of the pair (ranks i < j) and which member has the lower label; false = the reference skips it
 template <bool SMEM_LABEL>
-__device__ inline double eval_pair(const RankParams& p, int qid, int i, int j, int me, const double* s_score,
-                                   const float* s_label, const int* s_idx, const float* g_label, bool do_norm, int k,
-                                   float* lam, float* hes) {
+__device__ inline bool pair_terms(const RankParams& p, int qid, int i, int j, const double* s_score, const float* s_label,
+                                  const int* s_idx, const float* g_label, bool do_norm, int k, double* out_lambda,
+                                  double* out_hessian, int* out_low_rank) {
   const double score_i = s_score[i], score_j = s_score[j];
-  if (score_i == -INFINITY || score_j == -INFINITY) return 0.0;  // kMinScore, :320,354
+  if (score_i == -INFINITY || score_j == -INFINITY) return false;  // kMinScore, :320,354
   const float label_i = SMEM_LABEL ? s_label[i] : g_label[s_idx[i]];
   const float label_j = SMEM_LABEL ? s_label[j] : g_label[s_idx[j]];
-  if (label_i == label_j) return 0.0;
+  if (label_i == label_j) return false;
   const int t = p.target;
-  if (label_i > 0 && label_j > 0 && is_binary_target(t)) return 0.0;
+  if (label_i > 0 && label_j > 0 && is_binary_target(t)) return false;
   int high_rank, low_rank;
   float high_label_f, low_label_f;
   if (label_i > label_j) {
@@ -206,12 +206,27 @@ __device__ inline double eval_pair(const RankParams& p, int qid, int i, int j, i
       delta_pair = static_cast<double>(high_label_f) - static_cast<double>(low_label_f);
       break;
   }
-  if (delta_pair == 0) return 0.0;
+  if (delta_pair == 0) return false;
   if (do_norm) delta_pair /= (0.01f + fabs(delta_score));
   double p_lambda = get_sigmoid(p, delta_score);
   double p_hessian = p_lambda * (1.0f - p_lambda);
   p_lambda *= -p.sigmoid * delta_pair;
   p_hessian *= p.sigmoid * p.sigmoid * delta_pair;
+  *out_lambda = p_lambda;
+  *out_hessian = p_hessian;
+  *out_low_rank = low_rank;
+  return true;
+}
+
+// One pair (ranks i < j) seen from the document at rank `me` (== i or j).  Accumulates into (lam, hes) exactly
+// what the reference adds to that document (rank_objective.hpp:353-513); returns -2 * p_lambda (0 if skipped).
+template <bool SMEM_LABEL>
+__device__ inline double eval_pair(const RankParams& p, int qid, int i, int j, int me, const double* s_score,
+                                   const float* s_label, const int* s_idx, const float* g_label, bool do_norm, int k,
+                                   float* lam, float* hes) {
+  double p_lambda, p_hessian;
+  int low_rank;
+  if (!pair_terms<SMEM_LABEL>(p, qid, i, j, s_score, s_label, s_idx, g_label, do_norm, k, &p_lambda, &p_hessian, &low_rank)) return 0.0;
   if (me == low_rank) {
     *lam -= static_cast<float>(p_lambda);
   } else {
@@ -220,6 +235,7 @@ __device__ inline double eval_pair(const RankParams& p, int qid, int i, int j, i
   *hes += static_cast<float>(p_hessian);
   return -2 * p_lambda;
 }
+
 
 // std::nth_element of libstdc++ (introselect: median-of-3 Hoare partition, insertion sort below 4 elements) on the
 // index array with comparator score[a] > score[b], run by one thread.  The `precision` target orders documents
@@ -288,10 +304,12 @@ __device__ void device_nth_element(int* v, int n, int nth, const double* sc) {
 
 // smem layout: double score[n_pad]; int idx[n_pad]; float label[n_pad] (if SMEM_LABEL); double red[32];
 // double raw_score[n_pad] (precision target only)
+// pair_rows > 0: pair-parallel form (see below), with three more shared arrays behind the ones above:
+// float lam[n_pad]; float hes[n_pad]; float2 pair[pair_rows][n_pad]
 template <bool SMEM_LABEL>
 __global__ void lambdarank_kernel(RankParams p, const int* __restrict__ queries, int n_pad,
                                   const double* __restrict__ score, float* __restrict__ grad,
-                                  float* __restrict__ hess) {
+                                  float* __restrict__ hess, int pair_rows) {
   extern __shared__ unsigned char smem_raw[];
   double* s_score = reinterpret_cast<double*>(smem_raw);
   int* s_idx = reinterpret_cast<int*>(s_score + n_pad);
@@ -375,8 +393,88 @@ __global__ void lambdarank_kernel(RankParams p, const int* __restrict__ queries,
   const bool do_norm = p.norm && s_bw[0] != s_bw[1];
   const int i_end = is_truncated_i(t) ? min(cnt - 1, k) : cnt - 1;
 
-  // ---- gather: thread per document (rank r), pairs in the CPU's order
   double my_sum = 0.0;
+  if (pair_rows > 0) {
+    // ---- pair-parallel form.  The gather below lets the thread of a top-ranked document walk all of its pairs alone (a
+    // truncated target pairs the first k ranks with everybody: thread 0 of a 120-document query evaluates 119 pairs while
+    // most threads evaluate 30) and evaluates every pair twice, once per member.  Here the outer ranks are taken in chunks
+    // of pair_rows: (1) all threads evaluate the chunk's pairs once each, in parallel, into shared memory -- the signed
+    // float lambda as seen from member i, and the float hessian; (2) one thread per document adds the chunk's
+    // contributions to its running fp32 sums in the CPU's order: as the j member for ascending i, then (if it is in the
+    // chunk) as the i member for ascending j.  Chunks ascend, so the += sequence of every document is still the CPU's.
+    const size_t base = static_cast<size_t>(n_pad) * (8 + 4 + (SMEM_LABEL ? 4 : 0)) + 32 * 8 +
+                        (t == kPrecision ? static_cast<size_t>(n_pad) * 8 : 0);
+    float* s_lam = reinterpret_cast<float*>(smem_raw + base);
+    float* s_hes = s_lam + n_pad;
+    float2* s_pair = reinterpret_cast<float2*>(s_hes + n_pad);
+    for (int r = tid; r < cnt; r += nt) {
+      s_lam[r] = 0.f;
+      s_hes[r] = 0.f;
+    }
+    const bool a_from_k = t == kPrecision || t == kARPK || t == kLambdaGapSp || t == kLambdaGapXp || t == kLambdaGapSpp || t == kLambdaGapXpp;
+    for (int i0 = 0; i0 < i_end; i0 += pair_rows) {
+      const int i1 = min(i_end, i0 + pair_rows);
+      __syncthreads();  // the previous chunk's pairs have been consumed (and lam / hes are initialised)
+      for (int i = i0; i < i1; ++i) {
+        int js, je;
+        j_range(t, i, k, cnt, &js, &je);
+        float2* row = s_pair + static_cast<size_t>(i - i0) * cnt;
+        for (int j = js + tid; j < je; j += nt) {
+          double pl, ph;
+          int low;
+          float2 v = make_float2(0.f, 0.f);
+          if (pair_terms<SMEM_LABEL>(p, qid, i, j, s_score, s_label, s_idx, q_label, do_norm, k, &pl, &ph, &low)) {
+            const float fl = static_cast<float>(pl);
+            v.x = low == i ? -fl : fl;  // what member i adds; member j adds the opposite
+            v.y = static_cast<float>(ph);
+            my_sum += -2 * pl;
+          }
+          row[j] = v;
+        }
+      }
+      __syncthreads();
+      for (int r = tid; r < cnt; r += nt) {
+        float lam = s_lam[r], hes = s_hes[r];
+        // (a) as the j member: outer ranks i < r of this chunk whose inner range contains r, ascending i
+        int i_lo = 0, i_hi = min(r, i_end);
+        if (a_from_k) {
+          if (r < k) i_hi = 0;
+        } else if (t == kLambdaGapS) {
+          i_lo = max(0, r - k);
+          i_hi = r >= k ? min(i_hi, r - k + 1) : 0;
+        } else if (t == kLambdaGapX) {
+          i_hi = min(i_hi, r - k + 1);
+        }
+        i_lo = max(i_lo, i0);
+        i_hi = min(i_hi, i1);
+        for (int i = i_lo; i < i_hi; ++i) {
+          const float2 v = s_pair[static_cast<size_t>(i - i0) * cnt + r];
+          lam -= v.x;
+          hes += v.y;
+        }
+        // (b) as the i member: inner ranks j of outer rank r, ascending j
+        if (r >= i0 && r < i1) {
+          int js, je;
+          j_range(t, r, k, cnt, &js, &je);
+          const float2* row = s_pair + static_cast<size_t>(r - i0) * cnt;
+          for (int j = js; j < je; ++j) {
+            const float2 v = row[j];
+            lam += v.x;
+            hes += v.y;
+          }
+        }
+        s_lam[r] = lam;
+        s_hes[r] = hes;
+      }
+    }
+    __syncthreads();
+    for (int r = tid; r < cnt; r += nt) {
+      const int d = s_idx[r];
+      grad[start + d] = s_lam[r];
+      hess[start + d] = s_hes[r];
+    }
+  } else
+  // ---- gather: thread per document (rank r), pairs in the CPU's order
   for (int r = tid; r < cnt; r += nt) {
     float lam = 0.f, hes = 0.f;
     // (a) as the j member: outer ranks i < r whose inner range contains r, ascending i
@@ -609,12 +707,30 @@ void rank_objective_get_gradients(Objective* o, const double* score, float* grad
       if (!smem_label) fatal("lambdarank_target=precision supports queries of up to 8192 documents on this device");
       smem += static_cast<size_t>(pad) * 8;
     }
+    // pair-parallel form when a chunk of outer ranks fits shared memory beside the arrays: lam / hes + rows x pad float2
+    static const int pair_mode = [] {
+      const char* e = std::getenv("GBL_RANK_PAIRS");
+      return e == nullptr ? 1 : std::atoi(e);
+    }();
+    int pair_rows = 0;
+    if (pair_mode != 0) {
+      const size_t limit = (smem_label ? 200 : 220) * 1024;
+      const size_t extra = static_cast<size_t>(pad) * 8;  // lam + hes
+      const size_t per_row = static_cast<size_t>(pad) * 8;
+      // small classes: keep several CTAs per SM (<= 48 KB of pairs); large ones: whatever fits
+      const size_t budget = pad <= 128 ? 32 * 1024 : (pad <= 1024 ? 64 * 1024 : limit);
+      if (smem + extra + per_row <= limit) {
+        const size_t room = std::min(budget, limit - smem - extra);
+        pair_rows = static_cast<int>(std::max<size_t>(1, std::min<size_t>(64, room / per_row)));
+        smem += extra + static_cast<size_t>(pair_rows) * per_row;
+      }
+    }
     if (smem_label) {
       GBL_LAUNCH(lambdarank_kernel<true>, rs->class_count[c], kClassThreads[c], smem, cs, rs->p, rs->class_queries[c], pad,
-                 score, grad, hess);
+                 score, grad, hess, pair_rows);
     } else {
       GBL_LAUNCH(lambdarank_kernel<false>, rs->class_count[c], kClassThreads[c], smem, cs, rs->p, rs->class_queries[c], pad,
-                 score, grad, hess);
+                 score, grad, hess, pair_rows);
     }
     if (cs != s) {
       GBL_CUDA(cudaEventRecord(rs->join[k], cs));
