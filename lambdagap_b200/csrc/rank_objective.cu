@@ -51,6 +51,12 @@ struct RankParams {
   const float* weight;
 };
 
+// Query size classes: one launch per class, shared memory laid out for the class's longest query, so that the many short
+// queries keep many CTAs per SM and only the few very long ones pay for the big arrays.
+constexpr int kNumClasses = 7;
+static const int kClassLimit[kNumClasses] = {32, 64, 128, 256, 512, 1024, 16384};
+static const int kClassThreads[kNumClasses] = {32, 64, 128, 128, 256, 512, 1024};
+
 struct RankState {
   RankParams p{};
   double* sigmoid_table = nullptr;
@@ -59,9 +65,9 @@ struct RankState {
   double* inv_dcg = nullptr;
   double* inv_bdcg = nullptr;
   int* query_boundaries = nullptr;
-  int* class_queries[3] = {nullptr, nullptr, nullptr};  // query ids per size class
-  int class_count[3] = {0, 0, 0};
-  int class_pad[3] = {0, 0, 0};  // bitonic size (power of two) per class
+  int* class_queries[kNumClasses] = {};  // query ids per size class
+  int class_count[kNumClasses] = {};
+  int class_pad[kNumClasses] = {};  // array length (power of two) per class
   // the three size classes run side by side (the few very long queries would otherwise hold the GPU alone)
   cudaStream_t aux[2] = {nullptr, nullptr};
   cudaEvent_t fork = nullptr;
@@ -331,9 +337,15 @@ __global__ void lambdarank_kernel(RankParams p, const int* __restrict__ queries,
   // power of two (a 130-document query of the 129..1024 class sorts 256 elements, not 1024)
   int np = 2;
   while (np < cnt) np <<= 1;
+  // pair form: the labels are read here, beside the scores, into the (still unused) lam array and permuted from shared
+  // memory after the sort, instead of a dependent global gather behind it
+  const bool stage_label = SMEM_LABEL && pair_rows > 0;
+  float* s_stage = reinterpret_cast<float*>(smem_raw + static_cast<size_t>(n_pad) * (8 + 4 + (SMEM_LABEL ? 4 : 0)) + 32 * 8 +
+                                            (t == kPrecision ? static_cast<size_t>(n_pad) * 8 : 0));
   for (int i = tid; i < np; i += nt) {
     s_score[i] = i < cnt ? q_score[i] : -INFINITY;
     s_idx[i] = i;
+    if (stage_label && i < cnt) s_stage[i] = q_label[i];
   }
   __syncthreads();
   const bool sorted = !is_unsorted_target(t);
@@ -368,7 +380,7 @@ __global__ void lambdarank_kernel(RankParams p, const int* __restrict__ queries,
     }
   }
   if (SMEM_LABEL) {
-    for (int i = tid; i < cnt; i += nt) s_label[i] = q_label[s_idx[i]];
+    for (int i = tid; i < cnt; i += nt) s_label[i] = stage_label ? s_stage[s_idx[i]] : q_label[s_idx[i]];
   }
   // best / worst score (:268-298)
   if (tid == 0) {
@@ -447,6 +459,7 @@ __global__ void lambdarank_kernel(RankParams p, const int* __restrict__ queries,
         }
         i_lo = max(i_lo, i0);
         i_hi = min(i_hi, i1);
+#pragma unroll 4
         for (int i = i_lo; i < i_hi; ++i) {
           const float2 v = s_pair[static_cast<size_t>(i - i0) * cnt + r];
           lam -= v.x;
@@ -457,6 +470,7 @@ __global__ void lambdarank_kernel(RankParams p, const int* __restrict__ queries,
           int js, je;
           j_range(t, r, k, cnt, &js, &je);
           const float2* row = s_pair + static_cast<size_t>(r - i0) * cnt;
+#pragma unroll 8
           for (int j = js; j < je; ++j) {
             const float2 v = row[j];
             lam += v.x;
@@ -570,8 +584,6 @@ static T* upload(const std::vector<T>& v) {
   return d;
 }
 
-static const int kClassLimit[3] = {128, 1024, 16384};
-static const int kClassThreads[3] = {128, 256, 1024};
 
 void rank_objective_init(Objective* o, const gbl_objective_config* cfg, const float* label, const float* /*weight*/,
                          const int32_t* qb, int32_t num_queries) {
@@ -600,8 +612,8 @@ void rank_objective_init(Objective* o, const gbl_objective_config* cfg, const fl
     if (static_cast<size_t>(l) >= gain.size()) fatal("Label %zu is not less than the number of label mappings (%zu)", static_cast<size_t>(l), gain.size());
   }
   std::vector<double> inv_dcg(num_queries), inv_bdcg(num_queries);
-  std::vector<int> cls[3];
-  int max_len[3] = {0, 0, 0};
+  std::vector<int> cls[kNumClasses];
+  int max_len[kNumClasses] = {};
   const int k = cfg->lambdarank_truncation_level;
   for (int q = 0; q < num_queries; ++q) {
     const int n = qb[q + 1] - qb[q];
@@ -613,7 +625,8 @@ void rank_objective_init(Objective* o, const gbl_objective_config* cfg, const fl
     double b = cal_max_bdcg_at_k(k, label + qb[q], n, discount);
     if (b > 0.0) b = 1.0f / b;
     inv_bdcg[q] = b;
-    const int c = n <= kClassLimit[0] ? 0 : (n <= kClassLimit[1] ? 1 : 2);
+    int c = 0;
+    while (n > kClassLimit[c]) ++c;
     cls[c].push_back(q);
     max_len[c] = std::max(max_len[c], n);
   }
@@ -633,7 +646,7 @@ void rank_objective_init(Objective* o, const gbl_objective_config* cfg, const fl
   rs->inv_bdcg = upload(inv_bdcg);
   std::vector<int> qbv(qb, qb + num_queries + 1);
   rs->query_boundaries = upload(qbv);
-  for (int c = 0; c < 3; ++c) {
+  for (int c = 0; c < kNumClasses; ++c) {
     rs->class_count[c] = static_cast<int>(cls[c].size());
     rs->class_queries[c] = upload(cls[c]);
     int pad = 2;
@@ -672,7 +685,7 @@ void rank_objective_free(Objective* o) {
   cudaFree(rs->inv_dcg);
   cudaFree(rs->inv_bdcg);
   cudaFree(rs->query_boundaries);
-  for (int c = 0; c < 3; ++c) cudaFree(rs->class_queries[c]);
+  for (int c = 0; c < kNumClasses; ++c) cudaFree(rs->class_queries[c]);
   for (int a = 0; a < 2; ++a) {
     if (rs->aux[a]) cudaStreamDestroy(rs->aux[a]);
     if (rs->join[a]) cudaEventDestroy(rs->join[a]);
@@ -692,14 +705,16 @@ void rank_objective_get_gradients(Objective* o, const double* score, float* grad
     }
   }
   GBL_CUDA(cudaEventRecord(rs->fork, s));
-  // longest queries first and on their own streams: class 2 -> aux[0], class 0 -> aux[1], class 1 -> s
-  const int order[3] = {2, 0, 1};
+  // longest queries first; the classes go round the three streams so that one class's tail overlaps the next class
   cudaStream_t where[3] = {rs->aux[0], rs->aux[1], s};
-  for (int k = 0; k < 3; ++k) {
-    const int c = order[k];
+  bool used[3] = {false, false, false};
+  int turn = 0;
+  for (int c = kNumClasses - 1; c >= 0; --c) {
     if (rs->class_count[c] == 0) continue;
-    cudaStream_t cs = where[k];
-    if (cs != s) GBL_CUDA(cudaStreamWaitEvent(cs, rs->fork, 0));
+    const int w = turn++ % 3;
+    cudaStream_t cs = where[w];
+    if (cs != s && !used[w]) GBL_CUDA(cudaStreamWaitEvent(cs, rs->fork, 0));
+    used[w] = true;
     const int pad = rs->class_pad[c];
     const bool smem_label = pad <= 8192;
     size_t smem = static_cast<size_t>(pad) * (8 + 4 + (smem_label ? 4 : 0)) + 32 * 8;
@@ -717,11 +732,12 @@ void rank_objective_get_gradients(Objective* o, const double* score, float* grad
       const size_t limit = (smem_label ? 200 : 220) * 1024;
       const size_t extra = static_cast<size_t>(pad) * 8;  // lam + hes
       const size_t per_row = static_cast<size_t>(pad) * 8;
-      // small classes: keep several CTAs per SM (<= 48 KB of pairs); large ones: whatever fits
-      const size_t budget = pad <= 128 ? 32 * 1024 : (pad <= 1024 ? 64 * 1024 : limit);
+      // a CTA's share of the SM's shared memory when about 1200 threads are resident; the longest class takes what fits
+      const size_t share = pad <= 1024 ? static_cast<size_t>(kClassThreads[c]) * 192 : limit;
+      const size_t cap = rs->p.target <= kPrecision ? std::min(pad, rs->p.truncation_level) : pad;  // is_truncated_i
       if (smem + extra + per_row <= limit) {
-        const size_t room = std::min(budget, limit - smem - extra);
-        pair_rows = static_cast<int>(std::max<size_t>(1, std::min<size_t>(64, room / per_row)));
+        const size_t room = std::min(limit, std::max(share, smem + extra + per_row)) - smem - extra;
+        pair_rows = static_cast<int>(std::max<size_t>(1, std::min<size_t>(cap, room / per_row)));
         smem += extra + static_cast<size_t>(pair_rows) * per_row;
       }
     }
@@ -732,10 +748,11 @@ void rank_objective_get_gradients(Objective* o, const double* score, float* grad
       GBL_LAUNCH(lambdarank_kernel<false>, rs->class_count[c], kClassThreads[c], smem, cs, rs->p, rs->class_queries[c], pad,
                  score, grad, hess, pair_rows);
     }
-    if (cs != s) {
-      GBL_CUDA(cudaEventRecord(rs->join[k], cs));
-      GBL_CUDA(cudaStreamWaitEvent(s, rs->join[k], 0));
-    }
+  }
+  for (int w = 0; w < 2; ++w) {
+    if (!used[w]) continue;
+    GBL_CUDA(cudaEventRecord(rs->join[w], where[w]));
+    GBL_CUDA(cudaStreamWaitEvent(s, rs->join[w], 0));
   }
 }
 
