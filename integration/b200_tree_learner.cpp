@@ -18,12 +18,33 @@
 #include <LightGBM/utils/openmp_wrapper.h>
 
 #include <algorithm>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <thread>
 
 namespace LightGBM {
 
 namespace {
+// GBL_DROPIN_TIMING=1: wall-clock split of the learner's share of an iteration, printed when the learner is released
+struct StageClock {
+  bool on = std::getenv("GBL_DROPIN_TIMING") != nullptr && std::atoi(std::getenv("GBL_DROPIN_TIMING")) != 0;
+  double train_device = 0, train_host = 0, fetch = 0, add_score = 0, first_call = 0, last_return = 0;
+  int trees = 0;
+  static double Now() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+  void Report() const {
+    if (!on || trees == 0) return;
+    const double span = last_return - first_call;
+    // stderr, not Log: the split is wanted at verbosity -1 too
+    std::fprintf(stderr, "[B200 drop-in timing] %d trees, %.3f ms per iteration: upload + device tree %.3f, Tree::Split replay %.3f, "
+                 "leaf fetch %.3f, host score update %.3f, reference host code (gradients, bagging, metrics, ...) %.3f\n",
+                 trees, 1e3 * span / trees, 1e3 * train_device / trees, 1e3 * train_host / trees, 1e3 * fetch / trees,
+                 1e3 * add_score / trees, 1e3 * (span - train_device - train_host - fetch - add_score) / trees);
+  }
+};
+StageClock g_clock;
+
 void Check(int ret) {  // C-ABI status -> Log::Fatal, the reference's error convention (log.h:117-140)
   if (ret != 0) Log::Fatal("%s", gbl_last_error());
 }
@@ -36,6 +57,8 @@ B200TreeLearner::B200TreeLearner(const Config* config, int num_gpu) : config_(co
 B200TreeLearner::~B200TreeLearner() { Release(); }
 
 void B200TreeLearner::Release() {
+  g_clock.Report();
+  g_clock.trees = 0;
   for (const score_t* p : registered_) gbl_host_unregister(const_cast<score_t*>(p));
   registered_.clear();
   if (!leaf16_.empty()) gbl_host_unregister(leaf16_.data());
@@ -301,12 +324,29 @@ void B200TreeLearner::SetForcedSplit(const Json* forced_split_json) {
 
 Tree* B200TreeLearner::Train(const score_t* gradients, const score_t* hessians, bool /*is_first_tree*/) {
   // SerialTreeLearner::BeforeTrain: column sampling by tree (serial_tree_learner.cpp:293)
+  const double t_begin = StageClock::Now();
+  if (g_clock.trees == 0) g_clock.first_call = t_begin;
   col_sampler_->ResetByTree();
   if (config_->feature_fraction < 1.0) PushFeatureMask();
   int32_t quant_start = 0;
   if (quant_random_ready_) quant_start = quant_start_dist_(quant_start_engine_);  // gradient_discretizer.cpp:116
   // GBDT keeps its gradient / hessian vectors for the whole training (gbdt.cpp:849-865): page-lock them the first time
   // they are seen so that the per-tree upload runs at the PCIe rate instead of through a staging buffer
+  if (packed_gradients_ && bagging_) {
+    // position i of the packed arrays belongs to row bag_rows_[i]; rows outside the bag are never read by the learner
+    if (spread_gradients_.size() != static_cast<size_t>(num_data_)) {
+      spread_gradients_.assign(num_data_, 0.0f);
+      spread_hessians_.assign(num_data_, 0.0f);
+    }
+    const data_size_t cnt = static_cast<data_size_t>(bag_rows_.size());
+#pragma omp parallel for num_threads(OMP_NUM_THREADS()) schedule(static)
+    for (data_size_t i = 0; i < cnt; ++i) {
+      spread_gradients_[bag_rows_[i]] = gradients[i];
+      spread_hessians_[bag_rows_[i]] = hessians[i];
+    }
+    gradients = spread_gradients_.data();
+    hessians = spread_hessians_.data();
+  }
   for (const score_t* p : {gradients, hessians}) {
     if (registered_.insert(p).second && registered_.size() <= 256)
       gbl_host_register(const_cast<score_t*>(p), sizeof(score_t) * static_cast<size_t>(num_data_));
@@ -320,6 +360,8 @@ Tree* B200TreeLearner::Train(const score_t* gradients, const score_t* hessians, 
       throw std::runtime_error(gbl_last_error());
   });
   leaf_assignment_valid_ = false;
+  const double t_device = StageClock::Now();
+  g_clock.train_device += t_device - t_begin;
   const Shard& s0 = shards_[0];  // every rank of the data-parallel learner returns the same records (global counts)
   std::unique_ptr<Tree> tree(new Tree(config_->num_leaves, false, false));
   tree->SetLeafOutput(0, s0.result.root_output);  // serial_tree_learner.cpp:205-208
@@ -356,6 +398,7 @@ Tree* B200TreeLearner::Train(const score_t* gradients, const score_t* hessians, 
     for (int leaf = 0; leaf <= s0.result.num_splits; ++leaf) tree->SetLeafOutput(leaf, values[leaf]);
   }
   if (s0.result.num_splits == 0) Log::Warning("No further splits with positive gain, best gain: -inf");
+  g_clock.train_host += StageClock::Now() - t_device;
   return tree.release();
 }
 
@@ -369,11 +412,13 @@ Tree* B200TreeLearner::FitByExistingTree(const Tree*, const std::vector<int>&, c
   return nullptr;
 }
 
-void B200TreeLearner::SetBaggingData(const Dataset* /*subset*/, const data_size_t* used_indices, data_size_t num_data) {
+void B200TreeLearner::SetBaggingData(const Dataset* subset, const data_size_t* used_indices, data_size_t num_data) {
   // The reference may hand over a row-subset copy of the dataset (bagging_fraction <= 0.5, bagging.hpp:118-133); the
   // device keeps the full binned data, so the index list alone defines the bag -- same rows, same trees.
   leaf_assignment_valid_ = false;
   bagging_ = used_indices != nullptr && num_data > 0 && num_data < num_data_;
+  packed_gradients_ = bagging_ && subset != nullptr;
+  if (packed_gradients_) bag_rows_.assign(used_indices, used_indices + num_data);
   if (!bagging_) {
     for (Shard& s : shards_) Check(gbl_learner_set_bagging_data(s.learner, nullptr, 0));
     return;
@@ -415,20 +460,26 @@ void B200TreeLearner::AddPredictionToScore(const Tree* tree, double* out_score) 
   if (tree->num_leaves() <= 1) return;  // serial_tree_learner.h:101-103
   // out_score is the host ScoreUpdater's array in this build: leaf of every trained row from the device partition,
   // then score[row] += leaf_output (rows outside the bag carry -1; GBDT::UpdateScore walks the tree for them itself)
+  const double t_begin = StageClock::Now();
   FetchLeafAssignment();
+  const double t_fetch = StageClock::Now();
+  g_clock.fetch += t_fetch - t_begin;
   if (config_->num_leaves <= 65535) {
     const uint16_t* leaf = leaf16_.data();
 #pragma omp parallel for num_threads(OMP_NUM_THREADS()) schedule(static)
     for (data_size_t i = 0; i < num_data_; ++i) {
       if (leaf[i] != 0xFFFF) out_score[i] += tree->LeafOutput(leaf[i]);
     }
-    return;
-  }
-  const int32_t* leaf = leaf_of_row_.data();
+  } else {
+    const int32_t* leaf = leaf_of_row_.data();
 #pragma omp parallel for num_threads(OMP_NUM_THREADS()) schedule(static)
-  for (data_size_t i = 0; i < num_data_; ++i) {
-    if (leaf[i] >= 0) out_score[i] += tree->LeafOutput(leaf[i]);
+    for (data_size_t i = 0; i < num_data_; ++i) {
+      if (leaf[i] >= 0) out_score[i] += tree->LeafOutput(leaf[i]);
+    }
   }
+  g_clock.last_return = StageClock::Now();
+  g_clock.add_score += g_clock.last_return - t_fetch;
+  g_clock.trees += 1;
 }
 
 void B200TreeLearner::RenewTreeOutput(Tree* tree, const ObjectiveFunction* obj,

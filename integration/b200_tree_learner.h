@@ -94,6 +94,11 @@ class B200TreeLearner : public TreeLearner {
   int cat_params_[3] = {0, 0, 0};
   double cat_l2_ = -1.0, cat_smooth_ = -1.0;
   bool bagging_ = false;
+  // GOSS with top_rate + other_rate <= 0.5 trains on a row-subset copy (goss.hpp:101-108) and GBDT then hands Train the
+  // gradients of the bag's rows only, packed in bag order (gbdt.cpp:392-400): they are spread back to row positions here
+  bool packed_gradients_ = false;
+  std::vector<data_size_t> bag_rows_;
+  std::vector<score_t> spread_gradients_, spread_hessians_;
   mutable bool leaf_assignment_valid_ = false;
   mutable std::vector<int32_t> leaf_of_row_;
   mutable std::vector<uint16_t> leaf16_;   // page-locked 2-byte leaf ids (trees of at most 65535 leaves)

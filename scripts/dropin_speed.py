@@ -43,3 +43,4 @@ for _ in range(steps):
 dt = time.time() - t0
 print(json.dumps({"value": steps / dt, "unit": "iters/s", "ms_per_step": 1e3 * dt / steps, "rows": n, "params": params,
                   "what": "reference GBDT (host gradients / scores) + B200TreeLearner, LGBM_BoosterUpdateOneIter wall clock"}))
+check(lib.LGBM_BoosterFree(bst))  # releases the learner (prints the GBL_DROPIN_TIMING split)

@@ -68,8 +68,13 @@ CASES = {
     "regression_l1_renew": ("objective=regression_l1 num_leaves=31 learning_rate=0.1 verbose=-1 num_threads=4", 1e-5),
     "bagging": ("objective=binary num_leaves=31 learning_rate=0.1 bagging_fraction=0.7 bagging_freq=1 bagging_seed=5 "
                 "verbose=-1 num_threads=4", 1e-5),
-    "goss": ("objective=binary num_leaves=31 learning_rate=0.1 data_sample_strategy=goss top_rate=0.2 other_rate=0.1 "
-             "verbose=-1 num_threads=4", 1e-5),
+    # GOSS starts sampling at iteration 1 / learning_rate (goss.hpp:32-34): learning_rate=0.5 and six iterations, so that
+    # four of them are sampled.  top_rate + other_rate <= 0.5 makes the reference train on a row-subset copy and hand
+    # Train the bag's gradients packed in bag order (goss.hpp:101-108, gbdt.cpp:392-400); above 0.5 it passes the index list
+    "goss": ("objective=binary num_leaves=31 learning_rate=0.5 data_sample_strategy=goss top_rate=0.2 other_rate=0.1 "
+             "verbose=-1 num_threads=4", 1e-5, 6),
+    "goss_index_list": ("objective=binary num_leaves=31 learning_rate=0.5 data_sample_strategy=goss top_rate=0.4 "
+                        "other_rate=0.3 verbose=-1 num_threads=4", 1e-5, 6),
     # monotone constraints, method basic: +1 on column 0, -1 on column 1, +1 on column 4 (20 columns)
     "monotone_float": ("objective=binary num_leaves=63 learning_rate=0.1 verbose=-1 num_threads=4 "
                        "monotone_constraints=1,-1,0,0,1,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0", 1e-5),
@@ -88,11 +93,11 @@ CASES = {
 
 @pytest.mark.parametrize("name", sorted(CASES))
 def test_dropin_equals_reference_cpu(gpu, tmp_path, name):
-    params, rtol = CASES[name]
+    params, rtol = CASES[name][:2]
     X, y = H.make_binary(120_000, 20, seed=3, nan_frac=0.02, zero_frac=0.2)
     if "regression" in name:
         y = (X[:, 0] * 0.5 + np.nan_to_num(X[:, 2]) + 0.1 * np.random.default_rng(1).normal(size=len(y))).astype(np.float32)
-    iters = 4
+    iters = CASES[name][2] if len(CASES[name]) > 2 else 4
     ours, s_ours = _run_dropin(tmp_path, X, y, params + " device_type=cuda", iters)
     ref, s_ref = _run_reference(X, y, params, iters)
     _assert_models(ours, ref, rtol)
