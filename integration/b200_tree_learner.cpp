@@ -11,6 +11,8 @@
 //   RenewTreeOutput            SerialTreeLearner::RenewTreeOutput (:924-966)
 #include "b200_tree_learner.h"
 
+#include "b200_objective.h"
+
 #include <LightGBM/bin.h>
 #include <LightGBM/objective_function.h>
 #include <LightGBM/utils/common.h>
@@ -32,13 +34,15 @@ struct StageClock {
   bool on = std::getenv("GBL_DROPIN_TIMING") != nullptr && std::atoi(std::getenv("GBL_DROPIN_TIMING")) != 0;
   double train_device = 0, train_host = 0, fetch = 0, add_score = 0, first_call = 0, last_return = 0;
   int trees = 0;
+  bool warm = false;
   static double Now() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
   void Report() const {
     if (!on || trees == 0) return;
     const double span = last_return - first_call;
     // stderr, not Log: the split is wanted at verbosity -1 too
-    std::fprintf(stderr, "[B200 drop-in timing] %d trees, %.3f ms per iteration: upload + device tree %.3f, Tree::Split replay %.3f, "
-                 "leaf fetch %.3f, host score update %.3f, reference host code (gradients, bagging, metrics, ...) %.3f\n",
+    std::fprintf(stderr, "[B200 drop-in timing] %d trees after 3 warm-up trees, %.3f ms per iteration: Train (gradient upload unless "
+                 "they are in HBM already, device tree) %.3f, Tree::Split replay %.3f, leaf fetch %.3f, host score update %.3f, "
+                 "everything outside the learner (GBDT, objective: score upload + device gradients or host gradients) %.3f\n",
                  trees, 1e3 * span / trees, 1e3 * train_device / trees, 1e3 * train_host / trees, 1e3 * fetch / trees,
                  1e3 * add_score / trees, 1e3 * (span - train_device - train_host - fetch - add_score) / trees);
   }
@@ -347,14 +351,25 @@ Tree* B200TreeLearner::Train(const score_t* gradients, const score_t* hessians, 
     gradients = spread_gradients_.data();
     hessians = spread_hessians_.data();
   }
-  for (const score_t* p : {gradients, hessians}) {
-    if (registered_.insert(p).second && registered_.size() <= 256)
-      gbl_host_register(const_cast<score_t*>(p), sizeof(score_t) * static_cast<size_t>(num_data_));
+  // gradients the B200 objective of this library left in HBM (b200_objective.h): train from them, no upload
+  DeviceGradients on_device;
+  const bool from_device = shards_.size() == 1 && !(packed_gradients_ && bagging_) &&
+                           DeviceGradients::Take(gradients, hessians, num_data_, shards_[0].device, &on_device);
+  if (!from_device) {
+    for (const score_t* p : {gradients, hessians}) {
+      if (registered_.insert(p).second && registered_.size() <= 256)
+        gbl_host_register(const_cast<score_t*>(p), sizeof(score_t) * static_cast<size_t>(num_data_));
+    }
   }
   ForEachShard([&](Shard& s) {
     // one GPU: the reference's own offset; shards rotate inside their slice (see the warning in InitQuantRandom)
     const int32_t start = shards_.size() == 1 ? quant_start : quant_start % std::max<data_size_t>(1, s.count);
     if (quant_random_ready_ && gbl_learner_set_quant_random_start(s.learner, start) != 0) throw std::runtime_error(gbl_last_error());
+    if (from_device) {
+      if (gbl_learner_train(s.learner, on_device.dev_gradients, on_device.dev_hessians, &s.result, s.records.data()) != 0)
+        throw std::runtime_error(gbl_last_error());
+      return;
+    }
     // host gradients of this shard's rows -> HBM, one tree, split records back
     if (gbl_learner_train_host(s.learner, gradients + s.begin, hessians + s.begin, &s.result, s.records.data()) != 0)
       throw std::runtime_error(gbl_last_error());
@@ -480,6 +495,11 @@ void B200TreeLearner::AddPredictionToScore(const Tree* tree, double* out_score) 
   g_clock.last_return = StageClock::Now();
   g_clock.add_score += g_clock.last_return - t_fetch;
   g_clock.trees += 1;
+  if (!g_clock.warm && g_clock.trees == 3) {  // graph capture, page-locking and first-touch costs stay out of the split
+    g_clock.warm = true;
+    g_clock.trees = 0;
+    g_clock.train_device = g_clock.train_host = g_clock.fetch = g_clock.add_score = 0;
+  }
 }
 
 void B200TreeLearner::RenewTreeOutput(Tree* tree, const ObjectiveFunction* obj,

@@ -21,7 +21,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 DROPIN = os.path.join(ROOT, "integration", "_ref", "lib_lightgbm.so")
 
 
-def _run_dropin(tmp_path, X, y, params, iters, group=None, dataset_params="max_bin=255 verbose=-1"):
+def _run_dropin(tmp_path, X, y, params, iters, group=None, dataset_params="max_bin=255 verbose=-1", env=None):
     if not os.path.exists(DROPIN):
         pytest.fail("integration/_ref/lib_lightgbm.so missing: run __graft_entry__.build() where /root/reference exists")
     src, dst = str(tmp_path / "in.npz"), str(tmp_path / "out.npz")
@@ -30,7 +30,7 @@ def _run_dropin(tmp_path, X, y, params, iters, group=None, dataset_params="max_b
         arrays["group"] = group
     np.savez(src, **arrays)
     r = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "dropin_runner.py"), src, dst], capture_output=True, text=True,
-                       timeout=600)
+                       timeout=600, env=dict(os.environ, **(env or {})))
     assert r.returncode == 0, "drop-in run failed:\n" + r.stdout[-2000:] + r.stderr[-4000:]
     z = np.load(dst)
     return str(z["model"]), z["scores"]
@@ -104,6 +104,23 @@ def test_dropin_equals_reference_cpu(gpu, tmp_path, name):
     np.testing.assert_allclose(s_ours, s_ref, rtol=max(rtol, 1e-7), atol=1e-9)
 
 
+@pytest.mark.parametrize("route", ["host_objective", "device_objective_fills_host"])
+@pytest.mark.parametrize("name", ["binary_quantized", "regression_l2"])
+def test_dropin_gradient_routes(gpu, tmp_path, name, route):
+    """By default the drop-in computes regression / binary / lambdarank gradients on the device and trains from the device
+    copies (integration/b200_objective.cpp) -- that is what every other test in this file runs.  The two other routes must
+    give the same trees: the reference's host objective + upload, and the device objective that also fills GBDT's vectors."""
+    params, rtol = CASES[name][:2]
+    X, y = H.make_binary(120_000, 20, seed=3, nan_frac=0.02, zero_frac=0.2)
+    if "regression" in name:
+        y = (X[:, 0] * 0.5 + np.nan_to_num(X[:, 2]) + 0.1 * np.random.default_rng(1).normal(size=len(y))).astype(np.float32)
+    env = {"GBL_DROPIN_DEVICE_OBJECTIVE": "0"} if route == "host_objective" else {"GBL_DROPIN_FILL_HOST_GRADIENTS": "1"}
+    ours, s_ours = _run_dropin(tmp_path, X, y, params + " device_type=cuda", 4, env=env)
+    ref, s_ref = _run_reference(X, y, params, 4)
+    _assert_models(ours, ref, rtol)
+    np.testing.assert_allclose(s_ours, s_ref, rtol=max(rtol, 1e-7), atol=1e-9)
+
+
 def test_dropin_multiclass(gpu, tmp_path):
     """num_class trees per iteration: GBDT calls TreeLearner::Train once per class with offset gradient pointers."""
     rng = np.random.default_rng(5)
@@ -118,7 +135,8 @@ def test_dropin_multiclass(gpu, tmp_path):
 
 @pytest.mark.parametrize("target", ["ndcg", "lambdagap-x"])
 def test_dropin_lambdarank(gpu, tmp_path, target):
-    """The fork's lambdarank targets through the reference's own objective (host gradients) and the B200 learner."""
+    """The fork's lambdarank targets: device gradients (integration/b200_objective.cpp) and the B200 learner behind the
+    reference's GBDT, against the reference's own objective and CPU learner."""
     X, y, group = H.make_ranking(1500, 24, seed=11)
     params = ("objective=lambdarank lambdarank_target=%s lambdarank_truncation_level=10 num_leaves=31 learning_rate=0.1 "
               "min_data_in_leaf=20 verbose=-1 num_threads=4" % target)
