@@ -8,6 +8,9 @@
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
+#include <stdexcept>
+#include <string>
+#include <thread>
 #include <vector>
 
 namespace LightGBM {
@@ -46,10 +49,19 @@ int RankTargetIndex(const std::string& name) {
 
 std::mutex g_registry_mutex;
 std::vector<DeviceGradients> g_registry;
+std::vector<DeviceLayout> g_consumers;
 
 }  // namespace
 
 // ------------------------------------------------------------------------------------------- DeviceGradients
+bool DeviceLayout::operator==(const DeviceLayout& o) const {
+  if (num_data != o.num_data || num_parts != o.num_parts) return false;
+  for (int p = 0; p < num_parts; ++p) {
+    if (begin[p] != o.begin[p] || count[p] != o.count[p] || device[p] != o.device[p]) return false;
+  }
+  return true;
+}
+
 void DeviceGradients::Publish(const DeviceGradients& entry) {
   std::lock_guard<std::mutex> lock(g_registry_mutex);
   for (DeviceGradients& e : g_registry) {
@@ -68,15 +80,48 @@ void DeviceGradients::Withdraw(const score_t* host_gradients) {
                    g_registry.end());
 }
 
-bool DeviceGradients::Take(const score_t* host_gradients, const score_t* host_hessians, data_size_t num_data, int device_id,
-                           DeviceGradients* out) {
+bool DeviceGradients::Take(const score_t* host_gradients, const score_t* host_hessians, const DeviceLayout& layout,
+                           bool usable, DeviceGradients* out) {
   std::lock_guard<std::mutex> lock(g_registry_mutex);
   for (DeviceGradients& e : g_registry) {
     if (e.host_gradients != host_gradients) continue;
-    if (!e.fresh || e.host_hessians != host_hessians || e.num_data != num_data || e.device_id != device_id) return false;
+    if (!e.fresh) return false;
     e.fresh = false;
-    *out = e;
-    return true;
+    if (usable && e.host_hessians == host_hessians && e.layout == layout) {
+      *out = e;
+      return true;
+    }
+    if (!e.host_filled) {
+      Log::Fatal("B200 drop-in: the gradients of this iteration exist on the device only and the learner cannot train from "
+                 "that copy (row layout or sampling mode changed); set GBL_DROPIN_FILL_HOST_GRADIENTS=1");
+    }
+    return false;
+  }
+  return false;
+}
+
+void DeviceGradients::AddConsumer(const DeviceLayout& layout) {
+  std::lock_guard<std::mutex> lock(g_registry_mutex);
+  g_consumers.push_back(layout);
+}
+
+void DeviceGradients::RemoveConsumer(const DeviceLayout& layout) {
+  std::lock_guard<std::mutex> lock(g_registry_mutex);
+  for (size_t i = 0; i < g_consumers.size(); ++i) {
+    if (g_consumers[i] == layout) {
+      g_consumers.erase(g_consumers.begin() + i);
+      return;
+    }
+  }
+}
+
+bool DeviceGradients::FindConsumer(data_size_t num_data, DeviceLayout* out) {
+  std::lock_guard<std::mutex> lock(g_registry_mutex);
+  for (auto it = g_consumers.rbegin(); it != g_consumers.rend(); ++it) {  // the learner created last
+    if (it->num_data == num_data) {
+      *out = *it;
+      return true;
+    }
   }
   return false;
 }
@@ -108,37 +153,88 @@ ObjectiveFunction* ObjectiveFunction::CreateObjectiveFunction(const std::string&
 // ------------------------------------------------------------------------------------------- B200Objective
 B200Objective::B200Objective(ObjectiveFunction* host, const std::string& type, const Config& config)
     : host_(host), type_(type), config_(config) {
-  device_id_ = std::max(0, config.gpu_device_id);
-  // with num_gpu > 1 the learner's shards on the other GPUs read the host vectors
-  fill_host_ = config.num_gpu > 1 || EnvFlag("GBL_DROPIN_FILL_HOST_GRADIENTS", false);
+  force_fill_host_ = EnvFlag("GBL_DROPIN_FILL_HOST_GRADIENTS", false);
 }
 
 B200Objective::~B200Objective() { ReleaseDevice(); }
 
-void B200Objective::ReleaseDevice() {
+template <typename F>
+void B200Objective::ForEachPart(F fn) const {
+  const int R = layout_.num_parts;
+  if (R == 1) {
+    fn(0);
+    return;
+  }
+  // one host thread per GPU: the uploads run on all PCIe links at once
+  std::vector<std::string> errors(R);
+  std::vector<std::thread> threads;
+  for (int p = 0; p < R; ++p) {
+    threads.emplace_back([&, p] {
+      try {
+        fn(p);
+      } catch (const std::exception& ex) {
+        errors[p] = ex.what();
+        if (errors[p].empty()) errors[p] = "error";
+      }
+    });
+  }
+  for (std::thread& t : threads) t.join();
+  for (const std::string& e : errors) {
+    if (!e.empty()) Log::Fatal("%s", e.c_str());
+  }
+}
+
+void B200Objective::ReleaseDevice() const {
   if (published_ != nullptr) DeviceGradients::Withdraw(published_);
   published_ = nullptr;
   if (registered_score_ != nullptr) gbl_host_unregister(const_cast<double*>(registered_score_));
   registered_score_ = nullptr;
-  if (dev_ != nullptr) gbl_objective_free(dev_);
-  dev_ = nullptr;
-  for (void* p : {static_cast<void*>(score_dev_), static_cast<void*>(gradients_dev_), static_cast<void*>(hessians_dev_)}) {
-    if (p != nullptr) gbl_device_free(device_id_, p);
+  for (int p = 0; p < layout_.num_parts; ++p) {
+    Part& part = parts_[p];
+    if (part.objective != nullptr) gbl_objective_free(part.objective);
+    for (void* ptr : {static_cast<void*>(part.score), static_cast<void*>(part.gradients), static_cast<void*>(part.hessians)}) {
+      if (ptr != nullptr) gbl_device_free(layout_.device[p], ptr);
+    }
+    part = Part();
   }
-  score_dev_ = nullptr;
-  gradients_dev_ = nullptr;
-  hessians_dev_ = nullptr;
+  layout_ = DeviceLayout();
   on_device_ = false;
+  decided_ = false;
 }
 
 void B200Objective::Init(const Metadata& metadata, data_size_t num_data) {
   host_->Init(metadata, num_data);  // the reference's checks, label statistics, BoostFromScore inputs
   ReleaseDevice();
   num_data_ = num_data;
+  metadata_ = &metadata;  // owned by the Dataset, which outlives the objective's use of it (objective_function.h:24-29)
+}
+
+// The objective is initialised before GBDT creates its tree learner (c_api.cpp:174-186, gbdt.cpp:100-112), so the device
+// side is set up at the first GetGradients, when the learner has announced on which GPUs the rows live.
+void B200Objective::EnsureDevice() const {
+  if (decided_) return;
+  decided_ = true;
+  on_device_ = false;
+  const Metadata& md = *metadata_;
+  if (num_data_ <= 0 || md.label() == nullptr) return;
   // position-debiased lambdarank keeps per-position bias factors that GetGradients updates (rank_objective.hpp:91-120,
   // 123-172): host only
-  if (type_ == "lambdarank" && (metadata.positions() != nullptr || metadata.query_boundaries() == nullptr)) return;
-  if (num_data <= 0 || metadata.label() == nullptr) return;
+  if (type_ == "lambdarank" && (md.positions() != nullptr || md.query_boundaries() == nullptr)) return;
+  DeviceLayout lay;
+  fill_host_ = force_fill_host_;
+  if (!DeviceGradients::FindConsumer(num_data_, &lay)) {
+    // no learner takes device copies: one GPU computes, the host vectors are filled
+    lay = DeviceLayout();
+    lay.num_data = num_data_;
+    lay.num_parts = 1;
+    lay.begin[0] = 0;
+    lay.count[0] = num_data_;
+    lay.device[0] = std::max(0, config_.gpu_device_id);
+    fill_host_ = true;
+  }
+  // a query's documents may straddle two GPUs' row ranges: lambdarank stays on the host when the rows are sharded
+  if (lay.num_parts > 1 && type_ == "lambdarank") return;
+  layout_ = lay;
   gbl_objective_config c;
   std::memset(&c, 0, sizeof(c));
   c.kind = type_ == "regression" ? GBL_OBJ_REGRESSION_L2 : (type_ == "binary" ? GBL_OBJ_BINARY : GBL_OBJ_LAMBDARANK);
@@ -151,45 +247,79 @@ void B200Objective::Init(const Metadata& metadata, data_size_t num_data) {
   c.scale_pos_weight = config_.scale_pos_weight;
   c.num_label_gain = static_cast<int>(config_.label_gain.size());
   c.label_gain = config_.label_gain.empty() ? nullptr : config_.label_gain.data();
-  Check(gbl_objective_create(&c, num_data, metadata.label(), metadata.weights(),
-                             type_ == "lambdarank" ? metadata.query_boundaries() : nullptr,
-                             type_ == "lambdarank" ? metadata.num_queries() : 0, device_id_, &dev_));
-  const size_t n = static_cast<size_t>(num_data);
-  Check(gbl_device_malloc(device_id_, n * sizeof(double), reinterpret_cast<void**>(&score_dev_)));
-  Check(gbl_device_malloc(device_id_, n * sizeof(float), reinterpret_cast<void**>(&gradients_dev_)));
-  Check(gbl_device_malloc(device_id_, n * sizeof(float), reinterpret_cast<void**>(&hessians_dev_)));
+  // BinaryLogloss::Init derives need_train and the is_unbalance weights from the label counts of ALL rows
+  // (binary_objective.hpp:73-101); a part sees only its own
+  int64_t positive = 0, negative = 0;
+  if (type_ == "binary" && lay.num_parts > 1) {
+    const label_t* label = md.label();
+#pragma omp parallel for schedule(static) reduction(+ : positive, negative)
+    for (data_size_t i = 0; i < num_data_; ++i) {
+      if (label[i] > 0) {
+        ++positive;
+      } else {
+        ++negative;
+      }
+    }
+  }
+  const bool rank = type_ == "lambdarank";
+  ForEachPart([&](int p) {
+    Part& part = parts_[p];
+    const data_size_t b = lay.begin[p];
+    const size_t n = static_cast<size_t>(lay.count[p]);
+    const int dev = lay.device[p];
+    auto check = [](int ret) {
+      if (ret != 0) throw std::runtime_error(gbl_last_error());
+    };
+    check(gbl_objective_create(&c, lay.count[p], md.label() + b, md.weights() != nullptr ? md.weights() + b : nullptr,
+                               rank ? md.query_boundaries() : nullptr, rank ? md.num_queries() : 0, dev, &part.objective));
+    if (type_ == "binary" && lay.num_parts > 1) check(gbl_objective_set_label_counts(part.objective, positive, negative));
+    check(gbl_device_malloc(dev, n * sizeof(double), reinterpret_cast<void**>(&part.score)));
+    check(gbl_device_malloc(dev, n * sizeof(float), reinterpret_cast<void**>(&part.gradients)));
+    check(gbl_device_malloc(dev, n * sizeof(float), reinterpret_cast<void**>(&part.hessians)));
+  });
   on_device_ = true;
 }
 
 void B200Objective::GetGradients(const double* score, score_t* gradients, score_t* hessians) const {
+  EnsureDevice();
   if (!on_device_) {
     host_->GetGradients(score, gradients, hessians);
     return;
   }
-  const size_t n = static_cast<size_t>(num_data_);
   // GBDT's ScoreUpdater keeps one score array for the whole training (score_updater.hpp:24-48): page-lock it once
   if (registered_score_ != score) {
     if (registered_score_ != nullptr) gbl_host_unregister(const_cast<double*>(registered_score_));
-    gbl_host_register(const_cast<double*>(score), n * sizeof(double));  // failure = slower copies, nothing else
+    gbl_host_register(const_cast<double*>(score), static_cast<size_t>(num_data_) * sizeof(double));  // failure = slower copies
     registered_score_ = score;
   }
-  Check(gbl_memcpy_h2d(device_id_, score_dev_, score, n * sizeof(double)));
-  Check(gbl_objective_get_gradients(dev_, score_dev_, gradients_dev_, hessians_dev_, nullptr));
-  if (fill_host_) {
-    Check(gbl_memcpy_d2h(device_id_, gradients, gradients_dev_, n * sizeof(float)));
-    Check(gbl_memcpy_d2h(device_id_, hessians, hessians_dev_, n * sizeof(float)));
-  } else {
-    Check(gbl_device_synchronize(device_id_));  // the learner trains on its own stream
-  }
+  const bool fill = fill_host_;
+  ForEachPart([&](int p) {
+    const Part& part = parts_[p];
+    const data_size_t b = layout_.begin[p];
+    const size_t n = static_cast<size_t>(layout_.count[p]);
+    const int dev = layout_.device[p];
+    auto check = [](int ret) {
+      if (ret != 0) throw std::runtime_error(gbl_last_error());
+    };
+    check(gbl_memcpy_h2d(dev, part.score, score + b, n * sizeof(double)));
+    check(gbl_objective_get_gradients(part.objective, part.score, part.gradients, part.hessians, nullptr));
+    if (fill) {
+      check(gbl_memcpy_d2h(dev, gradients + b, part.gradients, n * sizeof(float)));
+      check(gbl_memcpy_d2h(dev, hessians + b, part.hessians, n * sizeof(float)));
+    }
+    check(gbl_device_synchronize(dev));  // the learner trains on its own stream
+  });
   if (published_ != nullptr && published_ != gradients) DeviceGradients::Withdraw(published_);
   DeviceGradients entry;
   entry.host_gradients = gradients;
   entry.host_hessians = hessians;
-  entry.dev_gradients = gradients_dev_;
-  entry.dev_hessians = hessians_dev_;
-  entry.num_data = num_data_;
-  entry.device_id = device_id_;
+  entry.layout = layout_;
+  for (int p = 0; p < layout_.num_parts; ++p) {
+    entry.dev_gradients[p] = parts_[p].gradients;
+    entry.dev_hessians[p] = parts_[p].hessians;
+  }
   entry.fresh = true;
+  entry.host_filled = fill;
   DeviceGradients::Publish(entry);
   published_ = gradients;
 }

@@ -10,7 +10,8 @@
 // vector GBDT hands over, runs the device objective (lambdagap_b200/csrc/objective.cu, rank_objective.cu) and leaves the
 // gradients in HBM.  B200TreeLearner::Train finds them through DeviceGradients (below) by the host pointers GBDT passes and
 // trains from the device copies, so neither the 10.5 M exp() of the host objective nor the upload of two float vectors per
-// tree happens; the host gradient vectors are filled as well whenever something else may read them.
+// tree happens; the host gradient vectors are filled as well whenever no learner has announced that it trains from the
+// device copies.  With num_gpu=N every GPU computes the gradients of its own rows (regression, binary).
 #ifndef LAMBDAGAP_B200_INTEGRATION_B200_OBJECTIVE_H_
 #define LAMBDAGAP_B200_INTEGRATION_B200_OBJECTIVE_H_
 
@@ -25,23 +26,40 @@
 
 namespace LightGBM {
 
-// Where the device copy of a host gradient vector lives.  One entry per B200Objective; the learner asks with the pointers
-// TreeLearner::Train receives.  An entry answers once per GetGradients call (Take clears `fresh`), so gradients the caller
-// changed or produced some other way are never replaced by a stale device copy.
+// How the rows are spread over GPUs: contiguous parts, one per GPU.  The learner announces its layout when it has built
+// its device data; the objective computes each part's gradients on that part's GPU.
+struct DeviceLayout {
+  static constexpr int kMaxParts = 16;
+  data_size_t num_data = 0;
+  int num_parts = 0;
+  data_size_t begin[kMaxParts] = {};
+  data_size_t count[kMaxParts] = {};
+  int device[kMaxParts] = {};
+  bool operator==(const DeviceLayout& o) const;
+};
+
+// Where the device copies of a host gradient vector live.  One entry per B200Objective; the learner asks with the
+// pointers TreeLearner::Train receives.  An entry answers once per GetGradients call (Take clears `fresh`), so gradients
+// the caller changed or produced some other way are never replaced by a stale device copy.
 struct DeviceGradients {
   const score_t* host_gradients = nullptr;
   const score_t* host_hessians = nullptr;
-  const float* dev_gradients = nullptr;
-  const float* dev_hessians = nullptr;
-  data_size_t num_data = 0;
-  int device_id = 0;
+  DeviceLayout layout;
+  const float* dev_gradients[DeviceLayout::kMaxParts] = {};  // part p: rows begin[p] .. begin[p] + count[p] - 1
+  const float* dev_hessians[DeviceLayout::kMaxParts] = {};
   bool fresh = false;
+  bool host_filled = false;  // the host vectors hold the same values
 
   static void Publish(const DeviceGradients& entry);
   static void Withdraw(const score_t* host_gradients);
-  // true and *out filled when a fresh device copy of exactly these vectors exists on `device_id`
-  static bool Take(const score_t* host_gradients, const score_t* host_hessians, data_size_t num_data, int device_id,
+  // A fresh entry for exactly these vectors and this layout: *out filled, true.  A fresh entry that cannot be used (other
+  // layout, `usable` false) is fine when the host vectors were filled too and fatal otherwise -- never a silent mix-up.
+  static bool Take(const score_t* host_gradients, const score_t* host_hessians, const DeviceLayout& layout, bool usable,
                    DeviceGradients* out);
+  // learners that will train from device copies
+  static void AddConsumer(const DeviceLayout& layout);
+  static void RemoveConsumer(const DeviceLayout& layout);
+  static bool FindConsumer(data_size_t num_data, DeviceLayout* out);
 };
 
 class B200Objective : public ObjectiveFunction {
@@ -77,19 +95,29 @@ class B200Objective : public ObjectiveFunction {
   std::string ToString() const override { return host_->ToString(); }
 
  private:
-  void ReleaseDevice();
+  struct Part {
+    gbl_objective* objective = nullptr;
+    double* score = nullptr;
+    float* gradients = nullptr;
+    float* hessians = nullptr;
+  };
+  void ReleaseDevice() const;
+  void EnsureDevice() const;  // first GetGradients: the learner exists by then and has announced its layout
+  template <typename F>
+  void ForEachPart(F fn) const;
 
   std::unique_ptr<ObjectiveFunction> host_;
   std::string type_;
   Config config_;
-  int device_id_ = 0;
   data_size_t num_data_ = 0;
-  bool on_device_ = false;     // false: every call goes to host_ (see Init for the cases)
-  bool fill_host_ = false;     // also copy the gradients into the caller's vectors
-  gbl_objective* dev_ = nullptr;
-  double* score_dev_ = nullptr;
-  float* gradients_dev_ = nullptr;
-  float* hessians_dev_ = nullptr;
+  const Metadata* metadata_ = nullptr;
+  bool force_fill_host_ = false;
+  // device state, built on first use
+  mutable bool decided_ = false;
+  mutable bool on_device_ = false;   // false: every call goes to host_ (see EnsureDevice for the cases)
+  mutable bool fill_host_ = false;   // also copy the gradients into the caller's vectors
+  mutable DeviceLayout layout_;
+  mutable Part parts_[DeviceLayout::kMaxParts];
   mutable const double* registered_score_ = nullptr;
   mutable const score_t* published_ = nullptr;
 };

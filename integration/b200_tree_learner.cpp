@@ -63,6 +63,8 @@ B200TreeLearner::~B200TreeLearner() { Release(); }
 void B200TreeLearner::Release() {
   g_clock.Report();
   g_clock.trees = 0;
+  if (announced_) DeviceGradients::RemoveConsumer(layout_);
+  announced_ = false;
   for (const score_t* p : registered_) gbl_host_unregister(const_cast<score_t*>(p));
   registered_.clear();
   if (!leaf16_.empty()) gbl_host_unregister(leaf16_.data());
@@ -283,6 +285,18 @@ void B200TreeLearner::Init(const Dataset* train_data, bool is_constant_hessian) 
   col_sampler_.reset(new ColSampler(config_));
   col_sampler_->SetTrainingData(train_data_);  // serial_tree_learner.cpp:59
   PushFeatureMask();
+  layout_ = DeviceLayout();
+  layout_.num_data = num_data_;
+  if (shards_.size() <= static_cast<size_t>(DeviceLayout::kMaxParts)) {
+    layout_.num_parts = static_cast<int>(shards_.size());
+    for (size_t r = 0; r < shards_.size(); ++r) {
+      layout_.begin[r] = shards_[r].begin;
+      layout_.count[r] = shards_[r].count;
+      layout_.device[r] = shards_[r].device;
+    }
+    DeviceGradients::AddConsumer(layout_);
+    announced_ = true;
+  }
   Log::Info("B200 tree learner: %d rows x %d features on %d GPU%s", num_data_, train_data_->num_features(),
             static_cast<int>(shards_.size()), shards_.size() > 1 ? "s (data-parallel, rows sharded)" : "");
 }
@@ -353,8 +367,8 @@ Tree* B200TreeLearner::Train(const score_t* gradients, const score_t* hessians, 
   }
   // gradients the B200 objective of this library left in HBM (b200_objective.h): train from them, no upload
   DeviceGradients on_device;
-  const bool from_device = shards_.size() == 1 && !(packed_gradients_ && bagging_) &&
-                           DeviceGradients::Take(gradients, hessians, num_data_, shards_[0].device, &on_device);
+  const bool from_device =
+      announced_ && DeviceGradients::Take(gradients, hessians, layout_, !(packed_gradients_ && bagging_), &on_device);
   if (!from_device) {
     for (const score_t* p : {gradients, hessians}) {
       if (registered_.insert(p).second && registered_.size() <= 256)
@@ -366,7 +380,9 @@ Tree* B200TreeLearner::Train(const score_t* gradients, const score_t* hessians, 
     const int32_t start = shards_.size() == 1 ? quant_start : quant_start % std::max<data_size_t>(1, s.count);
     if (quant_random_ready_ && gbl_learner_set_quant_random_start(s.learner, start) != 0) throw std::runtime_error(gbl_last_error());
     if (from_device) {
-      if (gbl_learner_train(s.learner, on_device.dev_gradients, on_device.dev_hessians, &s.result, s.records.data()) != 0)
+      const int part = static_cast<int>(&s - shards_.data());
+      if (gbl_learner_train(s.learner, on_device.dev_gradients[part], on_device.dev_hessians[part], &s.result,
+                            s.records.data()) != 0)
         throw std::runtime_error(gbl_last_error());
       return;
     }

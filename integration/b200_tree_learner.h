@@ -28,6 +28,7 @@
 #include <vector>
 
 #include "col_sampler.hpp"  // the reference's own ColSampler (src/treelearner/col_sampler.hpp)
+#include "b200_objective.h"
 #include "lambdagap_b200.h"
 
 namespace LightGBM {
@@ -94,6 +95,9 @@ class B200TreeLearner : public TreeLearner {
   int cat_params_[3] = {0, 0, 0};
   double cat_l2_ = -1.0, cat_smooth_ = -1.0;
   bool bagging_ = false;
+  // announced to DeviceGradients (b200_objective.h): Train takes the gradients the B200 objective left on these GPUs
+  DeviceLayout layout_;
+  bool announced_ = false;
   // GOSS with top_rate + other_rate <= 0.5 trains on a row-subset copy (goss.hpp:101-108) and GBDT then hands Train the
   // gradients of the bag's rows only, packed in bag order (gbdt.cpp:392-400): they are spread back to row positions here
   bool packed_gradients_ = false;
