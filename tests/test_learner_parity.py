@@ -41,6 +41,41 @@ def _run_pair(X, y, g, h, num_leaves, extra_ref="", quant=False, cfg_kw=None, lr
     return out
 
 
+@pytest.mark.parametrize("const_hess", [False, True])
+@pytest.mark.parametrize("features", [33, 36, 45, 48, 70])
+def test_ragged_last_tile_histograms(gpu, features, const_hess):
+    """Feature counts that leave a ragged last 32-feature tile (1, 4, 13, 16 features in it; 70 = two full tiles + 6), with
+    and without the constant-hessian count plane: root histogram and parent-minus-sibling, every feature of the last tile
+    and one of a full tile, against numpy; and the tree against the reference."""
+    X, y = H.make_binary(40000, features, seed=features, zero_frac=0.2, nan_frac=0.03)
+    g, h = _grads(y, 5)
+    if const_hess:
+        h = np.ones_like(h)
+    kw = dict(is_constant_hessian=1) if const_hess else {}
+    for num_leaves in (2, 3, 31):
+        o = _run_pair(X, y, g, h, num_leaves, cfg_kw=kw)
+        H.assert_tree_matches(o["ours"], o["ref"], shrinkage=0.1, rtol=1e-5)
+        if num_leaves == 31:
+            continue
+        lrn, recs = o["lrn"], o["recs"]
+        assign = lrn.leaf_assignment()
+        if num_leaves == 2:
+            leaf = 0 if recs[0]["left_count"] >= recs[0]["right_count"] else 1
+            m = np.ones(len(y), dtype=bool)
+        else:
+            leaf = 1 if recs[1]["leaf"] == 0 else 0
+            m = assign == leaf
+        first_of_last = (features - 1) // 32 * 32
+        for f in [3] + list(range(first_of_last, features)):
+            bins = o["cols"][f]
+            nb = o["infos"][f]["num_bin"]
+            hist = lrn.histogram(leaf, f)
+            eg = np.bincount(bins[m], weights=g[m].astype(np.float64), minlength=nb)[:nb]
+            eh = np.bincount(bins[m], weights=h[m].astype(np.float64), minlength=nb)[:nb]
+            np.testing.assert_allclose(hist[:, 0], eg, rtol=1e-6, atol=1e-5, err_msg="feature %d" % f)
+            np.testing.assert_allclose(hist[:, 1], eh, rtol=1e-6, atol=1e-5, err_msg="feature %d" % f)
+
+
 @pytest.mark.parametrize("quant", [True, False])
 @pytest.mark.parametrize("case", ["plain", "nan", "zero", "discrete"])
 def test_single_tree(gpu, quant, case):
