@@ -115,10 +115,10 @@ void DeviceGradients::RemoveConsumer(const DeviceLayout& layout) {
   }
 }
 
-bool DeviceGradients::FindConsumer(data_size_t num_data, DeviceLayout* out) {
+bool DeviceGradients::FindConsumer(data_size_t num_data, int num_parts, int device_id, DeviceLayout* out) {
   std::lock_guard<std::mutex> lock(g_registry_mutex);
-  for (auto it = g_consumers.rbegin(); it != g_consumers.rend(); ++it) {  // the learner created last
-    if (it->num_data == num_data) {
+  for (auto it = g_consumers.rbegin(); it != g_consumers.rend(); ++it) {
+    if (it->num_data == num_data && it->num_parts == num_parts && (num_parts > 1 || it->device[0] == device_id)) {
       *out = *it;
       return true;
     }
@@ -222,14 +222,15 @@ void B200Objective::EnsureDevice() const {
   if (type_ == "lambdarank" && (md.positions() != nullptr || md.query_boundaries() == nullptr)) return;
   DeviceLayout lay;
   fill_host_ = force_fill_host_;
-  if (!DeviceGradients::FindConsumer(num_data_, &lay)) {
+  const int device_id = std::max(0, config_.gpu_device_id);
+  if (!DeviceGradients::FindConsumer(num_data_, std::max(1, config_.num_gpu), device_id, &lay)) {
     // no learner takes device copies: one GPU computes, the host vectors are filled
     lay = DeviceLayout();
     lay.num_data = num_data_;
     lay.num_parts = 1;
     lay.begin[0] = 0;
     lay.count[0] = num_data_;
-    lay.device[0] = std::max(0, config_.gpu_device_id);
+    lay.device[0] = device_id;
     fill_host_ = true;
   }
   // a query's documents may straddle two GPUs' row ranges: lambdarank stays on the host when the rows are sharded

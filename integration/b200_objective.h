@@ -59,7 +59,8 @@ struct DeviceGradients {
   // learners that will train from device copies
   static void AddConsumer(const DeviceLayout& layout);
   static void RemoveConsumer(const DeviceLayout& layout);
-  static bool FindConsumer(data_size_t num_data, DeviceLayout* out);
+  // the learner created last over `num_data` rows on `num_parts` GPUs (one part: on GPU `device_id`)
+  static bool FindConsumer(data_size_t num_data, int num_parts, int device_id, DeviceLayout* out);
 };
 
 class B200Objective : public ObjectiveFunction {

@@ -67,8 +67,10 @@ void B200TreeLearner::Release() {
   announced_ = false;
   for (const score_t* p : registered_) gbl_host_unregister(const_cast<score_t*>(p));
   registered_.clear();
-  if (!leaf16_.empty()) gbl_host_unregister(leaf16_.data());
-  leaf16_.clear();
+  for (std::vector<uint16_t>& b : leaf16_buf_) {
+    if (!b.empty()) gbl_host_unregister(b.data());
+    b.clear();
+  }
   for (Shard& s : shards_) {
     if (s.learner != nullptr) gbl_learner_free(s.learner);
     s.learner = nullptr;
@@ -470,13 +472,15 @@ void B200TreeLearner::FetchLeafAssignment() const {
   if (leaf_assignment_valid_) return;
   if (config_->num_leaves <= 65535) {
     // 2-byte leaf ids into a page-locked buffer: a quarter of the bytes of the int32 form at the full PCIe rate
-    if (leaf16_.size() != static_cast<size_t>(num_data_)) {
-      if (!leaf16_.empty()) gbl_host_unregister(leaf16_.data());
-      leaf16_.assign(num_data_, 0xFFFF);
-      gbl_host_register(leaf16_.data(), sizeof(uint16_t) * leaf16_.size());  // failure = slower copies, nothing else
+    leaf16_turn_ ^= 1;
+    std::vector<uint16_t>& buf = leaf16_buf_[leaf16_turn_];
+    if (buf.size() != static_cast<size_t>(num_data_)) {
+      if (!buf.empty()) gbl_host_unregister(buf.data());
+      buf.assign(num_data_, 0xFFFF);
+      gbl_host_register(buf.data(), sizeof(uint16_t) * buf.size());  // failure = slower copies, nothing else
     }
     ForEachShard([&](Shard& s) {
-      if (gbl_learner_get_leaf_assignment_u16(s.learner, leaf16_.data() + s.begin) != 0) throw std::runtime_error(gbl_last_error());
+      if (gbl_learner_get_leaf_assignment_u16(s.learner, buf.data() + s.begin) != 0) throw std::runtime_error(gbl_last_error());
     });
   } else {
     leaf_of_row_.resize(num_data_);
@@ -496,7 +500,7 @@ void B200TreeLearner::AddPredictionToScore(const Tree* tree, double* out_score) 
   const double t_fetch = StageClock::Now();
   g_clock.fetch += t_fetch - t_begin;
   if (config_->num_leaves <= 65535) {
-    const uint16_t* leaf = leaf16_.data();
+    const uint16_t* leaf = leaf16().data();
 #pragma omp parallel for num_threads(OMP_NUM_THREADS()) schedule(static)
     for (data_size_t i = 0; i < num_data_; ++i) {
       if (leaf[i] != 0xFFFF) out_score[i] += tree->LeafOutput(leaf[i]);
@@ -527,7 +531,7 @@ void B200TreeLearner::RenewTreeOutput(Tree* tree, const ObjectiveFunction* obj,
   const int nl = tree->num_leaves();
   if (config_->num_leaves <= 65535) {  // one representation below: widen the 2-byte ids
     leaf_of_row_.resize(num_data_);
-    for (data_size_t i = 0; i < num_data_; ++i) leaf_of_row_[i] = leaf16_[i] == 0xFFFF ? -1 : static_cast<int32_t>(leaf16_[i]);
+    for (data_size_t i = 0; i < num_data_; ++i) leaf_of_row_[i] = leaf16()[i] == 0xFFFF ? -1 : static_cast<int32_t>(leaf16()[i]);
   }
   std::vector<data_size_t> begin(nl + 1, 0);
   for (data_size_t i = 0; i < num_data_; ++i) {

@@ -20,16 +20,29 @@ def check(r):
         raise RuntimeError(lib.LGBM_GetLastError().decode())
 
 
-cfg = dict(bench.HIGGS)
-rows = int(sys.argv[1]) if len(sys.argv) > 1 else cfg["rows"]
+# usage: dropin_speed.py [rows [extra params [higgs|mslr]]]
+workload = sys.argv[3] if len(sys.argv) > 3 else "higgs"
 extra = sys.argv[2] if len(sys.argv) > 2 else ""
-X, y = bench.gen_block(cfg, 0, rows)
+group = None
+if workload == "mslr":
+    cfg = dict(bench.MSLR)
+    Xd, y, group = bench.gen_mslr(0)
+    X = Xd.cpu().numpy()
+    del Xd
+else:
+    cfg = dict(bench.HIGGS)
+    rows = int(sys.argv[1]) if len(sys.argv) > 1 and int(sys.argv[1]) > 0 else cfg["rows"]
+    X, y = bench.gen_block(cfg, 0, rows)
 n, f = X.shape
 cores = os.cpu_count() or 1
 ds = ctypes.c_void_p()
 check(lib.LGBM_DatasetCreateFromMat(X.ctypes.data_as(ctypes.c_void_p), 0, ctypes.c_int32(n), ctypes.c_int32(f), 1,
                                     ("max_bin=255 verbose=-1 num_threads=%d" % cores).encode(), None, ctypes.byref(ds)))
 check(lib.LGBM_DatasetSetField(ds, b"label", y.ctypes.data_as(ctypes.c_void_p), ctypes.c_int(n), 0))
+if group is not None:
+    import numpy as np
+    group = np.ascontiguousarray(group, dtype=np.int32)
+    check(lib.LGBM_DatasetSetField(ds, b"group", group.ctypes.data_as(ctypes.c_void_p), ctypes.c_int(len(group)), 2))
 bst = ctypes.c_void_p()
 params = cfg["params"] + " device_type=cuda verbose=-1 num_threads=%d %s" % (cores, extra)
 check(lib.LGBM_BoosterCreate(ds, params.encode(), ctypes.byref(bst)))
