@@ -146,14 +146,17 @@ __device__ inline int plan_excl_scan(int v, int* s_warp, int& total) {
   __syncthreads();
   if (lane == 31) s_warp[warp] = x;
   __syncthreads();
-  int before = 0, tot = 0;
+  // the 32 warp totals: every warp scans them once with shuffles (lane k holds warp k's total)
+  static_assert(kPlanThreads / 32 == 32, "one lane per warp total");
+  int wt = s_warp[lane];
+  int ws = wt;
 #pragma unroll
-  for (int k = 0; k < kPlanThreads / 32; ++k) {
-    const int c = s_warp[k];
-    if (k < warp) before += c;
-    tot += c;
+  for (int o = 1; o < 32; o <<= 1) {
+    const int n = __shfl_up_sync(0xffffffffu, ws, o);
+    if (lane >= o) ws += n;
   }
-  total = tot;
+  total = __shfl_sync(0xffffffffu, ws, 31);
+  const int before = __shfl_sync(0xffffffffu, ws - wt, warp);
   return before + x - v;
 }
 
@@ -171,14 +174,25 @@ __global__ void __launch_bounds__(kPlanThreads) part_plan_kernel(LearnerDev d) {
     s_hist_rows = 0;
     s_part_rows = 0;
   }
-  // ---- exclusive prefix of the per-unit left counts (in place); unit_left[W] = total
+  // ---- exclusive prefix of the per-unit left counts (in place); unit_left[W] = total.  Eight consecutive units per
+  // thread and one block scan per 8 192 units: a level of the Higgs shape (5 127 units) is one pass instead of six.
   int carry = 0;
-  for (int base = 0; base < W; base += kPlanThreads) {
-    const int u = base + tid;
-    const int v = u < W ? d.unit_left[u] : 0;
+  constexpr int kPer = 8;
+  for (int base = 0; base < W; base += kPlanThreads * kPer) {
+    const int u0 = base + tid * kPer;
+    int v[kPer];
+#pragma unroll
+    for (int k = 0; k < kPer; ++k) v[k] = u0 + k < W ? d.unit_left[u0 + k] : 0;
+    int sum = 0;
+#pragma unroll
+    for (int k = 0; k < kPer; ++k) sum += v[k];
     int tot;
-    const int ex = plan_excl_scan(v, s_warp, tot);
-    if (u < W) d.unit_left[u] = carry + ex;
+    int run = carry + plan_excl_scan(sum, s_warp, tot);
+#pragma unroll
+    for (int k = 0; k < kPer; ++k) {
+      if (u0 + k < W) d.unit_left[u0 + k] = run;
+      run += v[k];
+    }
     carry += tot;
   }
   if (tid == 0) d.unit_left[W] = carry;
