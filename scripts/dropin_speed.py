@@ -1,4 +1,4 @@
-"""Speed of the drop-in library (integration/_ref/lib_lightgbm.so: the reference's GBDT on the host + the B200 tree learner)
+"""Speed of the drop-in library (integration/_ref/lib_lightgbm.so: the reference's GBDT on the host + the B200 objective and tree learner)
 on bench.py's headline workload, LGBM_BoosterUpdateOneIter wall clock.  Prints one JSON line.  Own process (see
 tests/dropin_runner.py for why)."""
 import ctypes
@@ -55,5 +55,5 @@ for _ in range(steps):
     check(lib.LGBM_BoosterUpdateOneIter(bst, ctypes.byref(fin)))
 dt = time.time() - t0
 print(json.dumps({"value": steps / dt, "unit": "iters/s", "ms_per_step": 1e3 * dt / steps, "rows": n, "params": params,
-                  "what": "reference GBDT (host gradients / scores) + B200TreeLearner, LGBM_BoosterUpdateOneIter wall clock"}))
+                  "what": "the reference library with B200Objective + B200TreeLearner compiled in (integration/_ref): its own GBDT, score array and model on the host, gradients and tree on the device; LGBM_BoosterUpdateOneIter wall clock"}))
 check(lib.LGBM_BoosterFree(bst))  # releases the learner (prints the GBL_DROPIN_TIMING split)
