@@ -21,13 +21,15 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 DROPIN = os.path.join(ROOT, "integration", "_ref", "lib_lightgbm.so")
 
 
-def _run_dropin(tmp_path, X, y, params, iters, group=None, dataset_params="max_bin=255 verbose=-1", env=None):
+def _run_dropin(tmp_path, X, y, params, iters, group=None, dataset_params="max_bin=255 verbose=-1", env=None, weight=None):
     if not os.path.exists(DROPIN):
         pytest.fail("integration/_ref/lib_lightgbm.so missing: run __graft_entry__.build() where /root/reference exists")
     src, dst = str(tmp_path / "in.npz"), str(tmp_path / "out.npz")
     arrays = dict(X=X, y=y, params=np.array(params), dataset_params=np.array(dataset_params), iters=np.array(iters))
     if group is not None:
         arrays["group"] = group
+    if weight is not None:
+        arrays["weight"] = weight
     np.savez(src, **arrays)
     r = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "dropin_runner.py"), src, dst], capture_output=True, text=True,
                        timeout=600, env=dict(os.environ, **(env or {})))
@@ -36,8 +38,8 @@ def _run_dropin(tmp_path, X, y, params, iters, group=None, dataset_params="max_b
     return str(z["model"]), z["scores"]
 
 
-def _run_reference(X, y, params, iters, group=None, dataset_params="max_bin=255 verbose=-1"):
-    ds = R.RefDataset(X, y, group=group, params=dataset_params + " force_col_wise=true")
+def _run_reference(X, y, params, iters, group=None, dataset_params="max_bin=255 verbose=-1", weight=None):
+    ds = R.RefDataset(X, y, group=group, weight=weight, params=dataset_params + " force_col_wise=true")
     b = R.RefBooster(ds, params + " device_type=cpu force_col_wise=true deterministic=true")
     for _ in range(iters):
         b.update()
@@ -119,6 +121,33 @@ def test_dropin_gradient_routes(gpu, tmp_path, name, route):
     ref, s_ref = _run_reference(X, y, params, 4)
     _assert_models(ours, ref, rtol)
     np.testing.assert_allclose(s_ours, s_ref, rtol=max(rtol, 1e-7), atol=1e-9)
+
+
+@pytest.mark.parametrize("case", ["binary_unbalance", "binary_scale_pos_weight", "regression", "lambdarank"])
+def test_dropin_device_objective_with_weights(gpu, tmp_path, case):
+    """Row weights, is_unbalance / scale_pos_weight label weights and a non-default sigmoid through the device objectives
+    of the drop-in (B200Objective: binary_objective.hpp:73-136, regression_objective.hpp:112-127, rank_objective.hpp:98-105)."""
+    rng = np.random.default_rng(17)
+    group = None
+    if case == "lambdarank":
+        X, y, group = H.make_ranking(1200, 16, seed=5)
+        params = ("objective=lambdarank lambdarank_truncation_level=8 sigmoid=1.5 num_leaves=31 learning_rate=0.1 "
+                  "min_data_in_leaf=20 verbose=-1 num_threads=4")
+    else:
+        X, y = H.make_binary(80_000, 12, seed=8, nan_frac=0.02)
+        if case == "regression":
+            y = (X[:, 0] - 0.5 * np.nan_to_num(X[:, 3]) + 0.1 * rng.normal(size=len(y))).astype(np.float32)
+            params = "objective=regression num_leaves=31 learning_rate=0.1 verbose=-1 num_threads=4"
+        elif case == "binary_unbalance":
+            y = (y * (rng.random(len(y)) < 0.3)).astype(np.float32)  # about 15 % positives
+            params = "objective=binary is_unbalance=true sigmoid=0.8 num_leaves=31 learning_rate=0.1 verbose=-1 num_threads=4"
+        else:
+            params = "objective=binary scale_pos_weight=2.5 num_leaves=31 learning_rate=0.1 verbose=-1 num_threads=4"
+    w = rng.uniform(0.5, 2.0, size=len(y)).astype(np.float32)
+    ours, s_ours = _run_dropin(tmp_path, X, y, params + " device_type=cuda", 4, group=group, weight=w)
+    ref, s_ref = _run_reference(X, y, params, 4, group=group, weight=w)
+    _assert_models(ours, ref, 1e-5)
+    np.testing.assert_allclose(s_ours, s_ref, rtol=1e-5, atol=1e-9)
 
 
 def test_dropin_multiclass(gpu, tmp_path):
