@@ -2,7 +2,7 @@
 behind its own TreeLearner interface) in a process of its own -- the oracle's lib_lightgbm.so exports the same C++
 symbols and must not share a process with it.  Usage (from tests/test_dropin_integration.py):
     python tests/dropin_runner.py IN.npz OUT.npz
-IN.npz: X, y, [group], params (str), dataset_params (str), iters (int).  OUT.npz: model (str), scores (raw train scores)."""
+IN.npz: X, y, [group], [weight], params (str), dataset_params (str), iters (int), [reset_after (int), reset_params (str)].  OUT.npz: model (str), scores (raw train scores)."""
 import ctypes
 import os
 import sys
@@ -39,7 +39,10 @@ def main():
     bst = ctypes.c_void_p()
     check(lib.LGBM_BoosterCreate(ds, ctypes.c_char_p(str(z["params"]).encode()), ctypes.byref(bst)))
     fin = ctypes.c_int(0)
-    for _ in range(int(z["iters"])):
+    reset_after = int(z["reset_after"]) if "reset_after" in z.files else -1
+    for it in range(int(z["iters"])):
+        if it == reset_after:  # LGBM_BoosterResetParameter (src/c_api.cpp:2053), e.g. a learning-rate schedule
+            check(lib.LGBM_BoosterResetParameter(bst, ctypes.c_char_p(str(z["reset_params"]).encode())))
         check(lib.LGBM_BoosterUpdateOneIter(bst, ctypes.byref(fin)))
     need = ctypes.c_int64(0)
     buf = ctypes.create_string_buffer(1 << 24)

@@ -21,7 +21,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 DROPIN = os.path.join(ROOT, "integration", "_ref", "lib_lightgbm.so")
 
 
-def _run_dropin(tmp_path, X, y, params, iters, group=None, dataset_params="max_bin=255 verbose=-1", env=None, weight=None):
+def _run_dropin(tmp_path, X, y, params, iters, group=None, dataset_params="max_bin=255 verbose=-1", env=None, weight=None,
+                reset=None):
     if not os.path.exists(DROPIN):
         pytest.fail("integration/_ref/lib_lightgbm.so missing: run __graft_entry__.build() where /root/reference exists")
     src, dst = str(tmp_path / "in.npz"), str(tmp_path / "out.npz")
@@ -30,6 +31,9 @@ def _run_dropin(tmp_path, X, y, params, iters, group=None, dataset_params="max_b
         arrays["group"] = group
     if weight is not None:
         arrays["weight"] = weight
+    if reset is not None:
+        arrays["reset_after"] = np.array(reset[0])
+        arrays["reset_params"] = np.array(reset[1])
     np.savez(src, **arrays)
     r = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "dropin_runner.py"), src, dst], capture_output=True, text=True,
                        timeout=600, env=dict(os.environ, **(env or {})))
@@ -148,6 +152,23 @@ def test_dropin_device_objective_with_weights(gpu, tmp_path, case):
     ref, s_ref = _run_reference(X, y, params, 4, group=group, weight=w)
     _assert_models(ours, ref, 1e-5)
     np.testing.assert_allclose(s_ours, s_ref, rtol=1e-5, atol=1e-9)
+
+
+def test_dropin_reset_parameter_mid_training(gpu, tmp_path):
+    """LGBM_BoosterResetParameter between iterations (a learning-rate schedule, then a change the device learner reads:
+    min_data_in_leaf and lambda_l2): TreeLearner::ResetConfig on the B200 learner, the device objective kept."""
+    X, y = H.make_binary(100_000, 16, seed=12, nan_frac=0.02)
+    params = "objective=binary num_leaves=31 learning_rate=0.2 verbose=-1 num_threads=4"
+    new = "learning_rate=0.05 min_data_in_leaf=200 lambda_l2=3.0"
+    ours, s_ours = _run_dropin(tmp_path, X, y, params + " device_type=cuda", 5, reset=(2, new))
+    ds = R.RefDataset(X, y, params="max_bin=255 verbose=-1 force_col_wise=true")
+    b = R.RefBooster(ds, params + " device_type=cpu force_col_wise=true deterministic=true")
+    for it in range(5):
+        if it == 2:
+            b.reset_parameter(new)
+        b.update()
+    _assert_models(ours, b.model_string(), 1e-5)
+    np.testing.assert_allclose(s_ours, b.train_scores(), rtol=1e-5, atol=1e-9)
 
 
 def test_dropin_multiclass(gpu, tmp_path):
