@@ -38,6 +38,19 @@ def main():
         check(lib.LGBM_DatasetSetField(ds, b"weight", w.ctypes.data_as(ctypes.c_void_p), ctypes.c_int(n), ctypes.c_int(0)))
     bst = ctypes.c_void_p()
     check(lib.LGBM_BoosterCreate(ds, ctypes.c_char_p(str(z["params"]).encode()), ctypes.byref(bst)))
+    vds = None
+    if "valid_X" in z.files:  # a validation set binned with the training set's mappers, LGBM_BoosterAddValidData
+        VX = np.ascontiguousarray(z["valid_X"], dtype=np.float32)
+        vy = np.ascontiguousarray(z["valid_y"], dtype=np.float32)
+        vds = ctypes.c_void_p()
+        check(lib.LGBM_DatasetCreateFromMat(VX.ctypes.data_as(ctypes.c_void_p), ctypes.c_int(0), ctypes.c_int32(VX.shape[0]),
+                                            ctypes.c_int32(VX.shape[1]), ctypes.c_int(1),
+                                            ctypes.c_char_p(str(z["dataset_params"]).encode()), ds, ctypes.byref(vds)))
+        check(lib.LGBM_DatasetSetField(vds, b"label", vy.ctypes.data_as(ctypes.c_void_p), ctypes.c_int(len(vy)), ctypes.c_int(0)))
+        if "valid_group" in z.files:
+            vg = np.ascontiguousarray(z["valid_group"], dtype=np.int32)
+            check(lib.LGBM_DatasetSetField(vds, b"group", vg.ctypes.data_as(ctypes.c_void_p), ctypes.c_int(len(vg)), ctypes.c_int(2)))
+        check(lib.LGBM_BoosterAddValidData(bst, vds))
     fin = ctypes.c_int(0)
     reset_after = int(z["reset_after"]) if "reset_after" in z.files else -1
     for it in range(int(z["iters"])):
@@ -56,7 +69,16 @@ def main():
     check(lib.LGBM_BoosterGetNumPredict(bst, ctypes.c_int(0), ctypes.byref(cnt)))
     scores = np.zeros(cnt.value, dtype=np.float64)
     check(lib.LGBM_BoosterGetPredict(bst, ctypes.c_int(0), ctypes.byref(cnt), scores.ctypes.data_as(ctypes.c_void_p)))
-    np.savez(dst, model=np.array(buf.value.decode()), scores=scores)
+    extra = {}
+    if vds is not None:
+        nm = ctypes.c_int(0)
+        check(lib.LGBM_BoosterGetEvalCounts(bst, ctypes.byref(nm)))
+        for idx, key in ((0, "train_eval"), (1, "valid_eval")):
+            vals = np.zeros(max(nm.value, 1), dtype=np.float64)
+            got = ctypes.c_int(0)
+            check(lib.LGBM_BoosterGetEval(bst, ctypes.c_int(idx), ctypes.byref(got), vals.ctypes.data_as(ctypes.c_void_p)))
+            extra[key] = vals[:got.value]
+    np.savez(dst, model=np.array(buf.value.decode()), scores=scores, **extra)
     check(lib.LGBM_BoosterFree(bst))
     check(lib.LGBM_DatasetFree(ds))
 

@@ -171,6 +171,43 @@ def test_dropin_reset_parameter_mid_training(gpu, tmp_path):
     np.testing.assert_allclose(s_ours, b.train_scores(), rtol=1e-5, atol=1e-9)
 
 
+@pytest.mark.parametrize("kind", ["binary", "lambdarank"])
+def test_dropin_validation_metrics(gpu, tmp_path, kind):
+    """A validation set and metrics through the reference's own LGBM_BoosterAddValidData / LGBM_BoosterGetEval in the
+    drop-in library: training and validation metric values after 5 iterations equal the reference's."""
+    if kind == "binary":
+        X, y = H.make_binary(60_000, 12, seed=31, nan_frac=0.02)
+        VX, vy = H.make_binary(20_000, 12, seed=32, nan_frac=0.02)
+        group = vgroup = None
+        params = "objective=binary metric=auc,binary_logloss num_leaves=31 learning_rate=0.1 verbose=-1 num_threads=4"
+    else:
+        X, y, group = H.make_ranking(900, 14, seed=33)
+        VX, vy, vgroup = H.make_ranking(300, 14, seed=34)
+        params = ("objective=lambdarank lambdarank_target=lambdagap-s-plus metric=ndcg eval_at=1,5 num_leaves=15 "
+                  "learning_rate=0.1 min_data_in_leaf=20 verbose=-1 num_threads=4")
+    src, dst = str(tmp_path / "in.npz"), str(tmp_path / "out.npz")
+    arrays = dict(X=X, y=y, params=np.array(params + " device_type=cuda"), dataset_params=np.array("max_bin=255 verbose=-1"),
+                  iters=np.array(5), valid_X=VX, valid_y=vy)
+    if group is not None:
+        arrays["group"] = group
+        arrays["valid_group"] = vgroup
+    np.savez(src, **arrays)
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "dropin_runner.py"), src, dst], capture_output=True, text=True,
+                       timeout=600)
+    assert r.returncode == 0, "drop-in run failed:\n" + r.stdout[-2000:] + r.stderr[-4000:]
+    z = np.load(dst)
+    ds = R.RefDataset(X, y, group=group, params="max_bin=255 verbose=-1 force_col_wise=true")
+    vds = R.RefDataset(VX, vy, group=vgroup, params="max_bin=255 verbose=-1", reference=ds)
+    b = R.RefBooster(ds, params + " device_type=cpu force_col_wise=true deterministic=true")
+    b.add_valid(vds)
+    for _ in range(5):
+        b.update()
+    _assert_models(str(z["model"]), b.model_string(), 1e-5)
+    np.testing.assert_allclose(z["train_eval"], b.eval(0), rtol=1e-6, atol=1e-9)
+    np.testing.assert_allclose(z["valid_eval"], b.eval(1), rtol=1e-6, atol=1e-9)
+    assert len(z["valid_eval"]) == 2
+
+
 def test_dropin_multiclass(gpu, tmp_path):
     """num_class trees per iteration: GBDT calls TreeLearner::Train once per class with offset gradient pointers."""
     rng = np.random.default_rng(5)
