@@ -94,6 +94,13 @@ CASES = {
                                  "monotone_constraints=-1,0,1,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0,0", 1e-9),
     "feature_fraction": ("objective=binary num_leaves=31 learning_rate=0.1 feature_fraction=0.6 feature_fraction_seed=9 "
                          "verbose=-1 num_threads=4", 1e-5),
+    # the reference's other boosting modes drive the same TreeLearner: DART drops and re-weights trees on the host score
+    # array between iterations (the device objective re-reads it every iteration), random forest trains every tree on
+    # the initial gradients with a fresh bag (host objective, as in the reference's own CUDA build)
+    "dart": ("objective=binary boosting=dart drop_rate=0.5 skip_drop=0.2 drop_seed=4 num_leaves=31 learning_rate=0.1 "
+             "verbose=-1 num_threads=4", 1e-5, 6),
+    "rf": ("objective=binary boosting=rf bagging_fraction=0.7 bagging_freq=1 bagging_seed=3 feature_fraction=0.8 "
+           "num_leaves=31 verbose=-1 num_threads=4", 1e-5, 4),
 }
 
 
