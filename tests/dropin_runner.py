@@ -2,7 +2,7 @@
 behind its own TreeLearner interface) in a process of its own -- the oracle's lib_lightgbm.so exports the same C++
 symbols and must not share a process with it.  Usage (from tests/test_dropin_integration.py):
     python tests/dropin_runner.py IN.npz OUT.npz
-IN.npz: X, y, [group], [weight], params (str), dataset_params (str), iters (int), [reset_after (int), reset_params (str)].  OUT.npz: model (str), scores (raw train scores)."""
+IN.npz: X, y, [group], [weight], params (str), dataset_params (str), iters (int), [reset_after (int), reset_params (str)], [rollback_after (int)].  OUT.npz: model (str), scores (raw train scores)."""
 import ctypes
 import os
 import sys
@@ -57,6 +57,8 @@ def main():
         if it == reset_after:  # LGBM_BoosterResetParameter (src/c_api.cpp:2053), e.g. a learning-rate schedule
             check(lib.LGBM_BoosterResetParameter(bst, ctypes.c_char_p(str(z["reset_params"]).encode())))
         check(lib.LGBM_BoosterUpdateOneIter(bst, ctypes.byref(fin)))
+        if "rollback_after" in z.files and it == int(z["rollback_after"]):  # LGBM_BoosterRollbackOneIter (src/c_api.cpp:2113)
+            check(lib.LGBM_BoosterRollbackOneIter(bst))
     need = ctypes.c_int64(0)
     buf = ctypes.create_string_buffer(1 << 24)
     check(lib.LGBM_BoosterSaveModelToString(bst, ctypes.c_int(0), ctypes.c_int(-1), ctypes.c_int(0), ctypes.c_int64(len(buf)),

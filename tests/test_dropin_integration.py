@@ -22,7 +22,7 @@ DROPIN = os.path.join(ROOT, "integration", "_ref", "lib_lightgbm.so")
 
 
 def _run_dropin(tmp_path, X, y, params, iters, group=None, dataset_params="max_bin=255 verbose=-1", env=None, weight=None,
-                reset=None):
+                reset=None, rollback_after=None):
     if not os.path.exists(DROPIN):
         pytest.fail("integration/_ref/lib_lightgbm.so missing: run __graft_entry__.build() where /root/reference exists")
     src, dst = str(tmp_path / "in.npz"), str(tmp_path / "out.npz")
@@ -34,6 +34,8 @@ def _run_dropin(tmp_path, X, y, params, iters, group=None, dataset_params="max_b
     if reset is not None:
         arrays["reset_after"] = np.array(reset[0])
         arrays["reset_params"] = np.array(reset[1])
+    if rollback_after is not None:
+        arrays["rollback_after"] = np.array(rollback_after)
     np.savez(src, **arrays)
     r = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "dropin_runner.py"), src, dst], capture_output=True, text=True,
                        timeout=600, env=dict(os.environ, **(env or {})))
@@ -213,6 +215,22 @@ def test_dropin_validation_metrics(gpu, tmp_path, kind):
     np.testing.assert_allclose(z["train_eval"], b.eval(0), rtol=1e-6, atol=1e-9)
     np.testing.assert_allclose(z["valid_eval"], b.eval(1), rtol=1e-6, atol=1e-9)
     assert len(z["valid_eval"]) == 2
+
+
+def test_dropin_rollback_one_iter(gpu, tmp_path):
+    """LGBM_BoosterRollbackOneIter after the third iteration: the host score array loses that tree (GBDT::RollbackOneIter,
+    gbdt.cpp:447-466) and the next gradients -- computed on the device from the uploaded scores -- must see it."""
+    X, y = H.make_binary(80_000, 14, seed=41, nan_frac=0.02)
+    params = "objective=binary num_leaves=31 learning_rate=0.2 verbose=-1 num_threads=4"
+    ours, s_ours = _run_dropin(tmp_path, X, y, params + " device_type=cuda", 5, rollback_after=2)
+    ds = R.RefDataset(X, y, params="max_bin=255 verbose=-1 force_col_wise=true")
+    b = R.RefBooster(ds, params + " device_type=cpu force_col_wise=true deterministic=true")
+    for it in range(5):
+        b.update()
+        if it == 2:
+            R._check(R.lib().LGBM_BoosterRollbackOneIter(b.handle))
+    _assert_models(ours, b.model_string(), 1e-5)
+    np.testing.assert_allclose(s_ours, b.train_scores(), rtol=1e-5, atol=1e-9)
 
 
 def test_dropin_multiclass(gpu, tmp_path):
