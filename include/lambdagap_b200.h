@@ -34,6 +34,7 @@ extern "C" {
 #define GBL_OBJ_REGRESSION_L2 0
 #define GBL_OBJ_BINARY 1
 #define GBL_OBJ_LAMBDARANK 2
+#define GBL_OBJ_MULTICLASS 3 /* MulticlassSoftmax, src/objective/multiclass_objective.hpp:25-170 */
 
 /* metric kinds, src/metric/metric.cpp:20-133 (Metric::CreateMetric) */
 #define GBL_METRIC_L2 0
@@ -325,7 +326,9 @@ typedef struct gbl_objective_config {
   double sigmoid;                      /* 1.0 */
   double lambdagap_weight;             /* 1.0 */
   int32_t is_unbalance;                /* binary */
-  int32_t reserved;
+  int32_t num_class;                   /* multiclass (GBL_OBJ_MULTICLASS): >= 2; scores / gradients / hessians are
+                                          class-major arrays of num_class * num_data entries like the reference's
+                                          (multiclass_objective.hpp:84-86); 0 for every other kind */
   double scale_pos_weight;             /* binary, 1.0 */
   int32_t num_label_gain;
   int32_t reserved2;

@@ -5,6 +5,7 @@
 #include <LightGBM/utils/log.h>
 
 #include <algorithm>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
@@ -84,11 +85,20 @@ bool DeviceGradients::Take(const score_t* host_gradients, const score_t* host_he
                            bool usable, DeviceGradients* out) {
   std::lock_guard<std::mutex> lock(g_registry_mutex);
   for (DeviceGradients& e : g_registry) {
-    if (e.host_gradients != host_gradients) continue;
-    if (!e.fresh) return false;
-    e.fresh = false;
-    if (usable && e.host_hessians == host_hessians && e.layout == layout) {
+    // which class block of the entry's vectors do the pointers address?
+    const data_size_t n = e.layout.num_data;
+    if (host_gradients < e.host_gradients || n <= 0) continue;
+    const size_t off = static_cast<size_t>(host_gradients - e.host_gradients);
+    if (off % static_cast<size_t>(n) != 0 || off / static_cast<size_t>(n) >= static_cast<size_t>(e.num_class)) continue;
+    const int k = static_cast<int>(off / static_cast<size_t>(n));
+    if (((e.fresh >> k) & 1ull) == 0) return false;
+    e.fresh &= ~(1ull << k);
+    if (usable && host_hessians == e.host_hessians + off && e.layout == layout) {
       *out = e;
+      for (int p = 0; p < e.layout.num_parts; ++p) {
+        out->dev_gradients[p] = e.dev_gradients[p] + static_cast<size_t>(k) * e.layout.count[p];
+        out->dev_hessians[p] = e.dev_hessians[p] + static_cast<size_t>(k) * e.layout.count[p];
+      }
       return true;
     }
     if (!e.host_filled) {
@@ -136,6 +146,7 @@ bool B200Objective::Supported(const std::string& type, const Config& config) {
   if (type == "regression") return !config.reg_sqrt;
   if (type == "binary") return true;
   if (type == "lambdarank") return RankTargetIndex(config.lambdarank_target) >= 0;
+  if (type == "multiclass") return config.num_class >= 2 && config.num_class <= 64;  // one `fresh` bit per class
   return false;
 }
 
@@ -154,6 +165,7 @@ ObjectiveFunction* ObjectiveFunction::CreateObjectiveFunction(const std::string&
 B200Objective::B200Objective(ObjectiveFunction* host, const std::string& type, const Config& config)
     : host_(host), type_(type), config_(config) {
   force_fill_host_ = EnvFlag("GBL_DROPIN_FILL_HOST_GRADIENTS", false);
+  num_class_ = type == "multiclass" ? config.num_class : 1;
 }
 
 B200Objective::~B200Objective() { ReleaseDevice(); }
@@ -238,7 +250,9 @@ void B200Objective::EnsureDevice() const {
   layout_ = lay;
   gbl_objective_config c;
   std::memset(&c, 0, sizeof(c));
-  c.kind = type_ == "regression" ? GBL_OBJ_REGRESSION_L2 : (type_ == "binary" ? GBL_OBJ_BINARY : GBL_OBJ_LAMBDARANK);
+  c.kind = type_ == "regression" ? GBL_OBJ_REGRESSION_L2
+                                 : (type_ == "binary" ? GBL_OBJ_BINARY : (type_ == "multiclass" ? GBL_OBJ_MULTICLASS : GBL_OBJ_LAMBDARANK));
+  c.num_class = type_ == "multiclass" ? num_class_ : 0;
   c.lambdarank_target = std::max(0, RankTargetIndex(config_.lambdarank_target));
   c.lambdarank_truncation_level = config_.lambdarank_truncation_level;
   c.lambdarank_norm = config_.lambdarank_norm ? 1 : 0;
@@ -274,11 +288,17 @@ void B200Objective::EnsureDevice() const {
     check(gbl_objective_create(&c, lay.count[p], md.label() + b, md.weights() != nullptr ? md.weights() + b : nullptr,
                                rank ? md.query_boundaries() : nullptr, rank ? md.num_queries() : 0, dev, &part.objective));
     if (type_ == "binary" && lay.num_parts > 1) check(gbl_objective_set_label_counts(part.objective, positive, negative));
-    check(gbl_device_malloc(dev, n * sizeof(double), reinterpret_cast<void**>(&part.score)));
-    check(gbl_device_malloc(dev, n * sizeof(float), reinterpret_cast<void**>(&part.gradients)));
-    check(gbl_device_malloc(dev, n * sizeof(float), reinterpret_cast<void**>(&part.hessians)));
+    const size_t nk = n * static_cast<size_t>(num_class_);
+    check(gbl_device_malloc(dev, nk * sizeof(double), reinterpret_cast<void**>(&part.score)));
+    check(gbl_device_malloc(dev, nk * sizeof(float), reinterpret_cast<void**>(&part.gradients)));
+    check(gbl_device_malloc(dev, nk * sizeof(float), reinterpret_cast<void**>(&part.hessians)));
   });
   on_device_ = true;
+  Log::Info("B200 objective: %s gradients on %d GPU%s%s", type_.c_str(), lay.num_parts, lay.num_parts > 1 ? "s" : "",
+            fill_host_ ? ", host vectors filled as well" : ", kept in HBM for the learner");
+  if (EnvFlag("GBL_DROPIN_TIMING", false))
+    std::fprintf(stderr, "[B200 drop-in] objective %s: device, %d part(s), %d class block(s), host vectors filled: %s\n",
+                 type_.c_str(), lay.num_parts, num_class_, fill_host_ ? "yes" : "no");
 }
 
 void B200Objective::GetGradients(const double* score, score_t* gradients, score_t* hessians) const {
@@ -290,7 +310,7 @@ void B200Objective::GetGradients(const double* score, score_t* gradients, score_
   // GBDT's ScoreUpdater keeps one score array for the whole training (score_updater.hpp:24-48): page-lock it once
   if (registered_score_ != score) {
     if (registered_score_ != nullptr) gbl_host_unregister(const_cast<double*>(registered_score_));
-    gbl_host_register(const_cast<double*>(score), static_cast<size_t>(num_data_) * sizeof(double));  // failure = slower copies
+    gbl_host_register(const_cast<double*>(score), static_cast<size_t>(num_data_) * num_class_ * sizeof(double));  // failure = slower copies
     registered_score_ = score;
   }
   const bool fill = fill_host_;
@@ -302,11 +322,15 @@ void B200Objective::GetGradients(const double* score, score_t* gradients, score_
     auto check = [](int ret) {
       if (ret != 0) throw std::runtime_error(gbl_last_error());
     };
-    check(gbl_memcpy_h2d(dev, part.score, score + b, n * sizeof(double)));
+    const size_t total = static_cast<size_t>(num_data_);
+    for (int k = 0; k < num_class_; ++k)  // class block k of the host array -> class block k of the part
+      check(gbl_memcpy_h2d(dev, part.score + k * n, score + k * total + b, n * sizeof(double)));
     check(gbl_objective_get_gradients(part.objective, part.score, part.gradients, part.hessians, nullptr));
     if (fill) {
-      check(gbl_memcpy_d2h(dev, gradients + b, part.gradients, n * sizeof(float)));
-      check(gbl_memcpy_d2h(dev, hessians + b, part.hessians, n * sizeof(float)));
+      for (int k = 0; k < num_class_; ++k) {
+        check(gbl_memcpy_d2h(dev, gradients + k * total + b, part.gradients + k * n, n * sizeof(float)));
+        check(gbl_memcpy_d2h(dev, hessians + k * total + b, part.hessians + k * n, n * sizeof(float)));
+      }
     }
     check(gbl_device_synchronize(dev));  // the learner trains on its own stream
   });
@@ -319,7 +343,8 @@ void B200Objective::GetGradients(const double* score, score_t* gradients, score_
     entry.dev_gradients[p] = parts_[p].gradients;
     entry.dev_hessians[p] = parts_[p].hessians;
   }
-  entry.fresh = true;
+  entry.num_class = num_class_;
+  entry.fresh = num_class_ >= 64 ? ~0ull : ((1ull << num_class_) - 1ull);
   entry.host_filled = fill;
   DeviceGradients::Publish(entry);
   published_ = gradients;

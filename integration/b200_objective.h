@@ -47,7 +47,11 @@ struct DeviceGradients {
   DeviceLayout layout;
   const float* dev_gradients[DeviceLayout::kMaxParts] = {};  // part p: rows begin[p] .. begin[p] + count[p] - 1
   const float* dev_hessians[DeviceLayout::kMaxParts] = {};
-  bool fresh = false;
+  // multiclass: the host vectors hold num_class blocks of num_data entries (class-major, multiclass_objective.hpp:84-86),
+  // GBDT calls Train once per class with the block's address (gbdt.cpp:385-402); part p's device arrays hold num_class
+  // blocks of count[p] entries.  One bit per class that has not been trained from yet.
+  int num_class = 1;
+  unsigned long long fresh = 0;
   bool host_filled = false;  // the host vectors hold the same values
 
   static void Publish(const DeviceGradients& entry);
@@ -117,6 +121,7 @@ class B200Objective : public ObjectiveFunction {
   mutable bool decided_ = false;
   mutable bool on_device_ = false;   // false: every call goes to host_ (see EnsureDevice for the cases)
   mutable bool fill_host_ = false;   // also copy the gradients into the caller's vectors
+  int num_class_ = 1;
   mutable DeviceLayout layout_;
   mutable Part parts_[DeviceLayout::kMaxParts];
   mutable const double* registered_score_ = nullptr;

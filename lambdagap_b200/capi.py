@@ -65,7 +65,7 @@ class ObjectiveConfig(ctypes.Structure):
     _fields_ = [("kind", ctypes.c_int32), ("lambdarank_target", ctypes.c_int32),
                 ("lambdarank_truncation_level", ctypes.c_int32), ("lambdarank_norm", ctypes.c_int32),
                 ("sigmoid", ctypes.c_double), ("lambdagap_weight", ctypes.c_double), ("is_unbalance", ctypes.c_int32),
-                ("reserved", ctypes.c_int32), ("scale_pos_weight", ctypes.c_double), ("num_label_gain", ctypes.c_int32),
+                ("num_class", ctypes.c_int32), ("scale_pos_weight", ctypes.c_double), ("num_label_gain", ctypes.c_int32),
                 ("reserved2", ctypes.c_int32), ("label_gain", ctypes.POINTER(ctypes.c_double))]
 
 

@@ -2,6 +2,8 @@
 //
 // Reference: RegressionL2loss::GetGradients   src/objective/regression_objective.hpp:112-127
 //            BinaryLogloss::Init/GetGradients src/objective/binary_objective.hpp:58-136, BoostFromScore :139-166
+//            MulticlassSoftmax::GetGradients  src/objective/multiclass_objective.hpp:84-133, Common::Softmax
+//                                             include/LightGBM/utils/common.h:580-594
 //            (lambdarank lives in rank_objective.cu)
 // Arithmetic follows the reference: fp64 per row, results cast to score_t = float.
 #include <cmath>
@@ -43,6 +45,34 @@ __global__ void __launch_bounds__(256) binary_gradients_kernel(const double* __r
     } else {
       grad[i] = static_cast<float>(response * label_weight * weight[i]);
       hess[i] = static_cast<float>(abs_response * (sigmoid - abs_response) * label_weight * weight[i]);
+    }
+  }
+}
+
+// Softmax over the row's K class scores (class-major arrays, entry k * n + i), then p - [label == k] and
+// factor * p * (1 - p) with factor = K / (K - 1) (multiclass_objective.hpp:31).  One thread per row; the K scores are
+// read three times (maximum, sum of exponentials, results) instead of being held in a per-thread array of unknown size.
+__global__ void __launch_bounds__(256) multiclass_gradients_kernel(const double* __restrict__ score,
+                                                                   const float* __restrict__ label,
+                                                                   const float* __restrict__ weight, int n, int num_class,
+                                                                   double factor, float* __restrict__ grad,
+                                                                   float* __restrict__ hess) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    double wmax = score[i];
+    for (int k = 1; k < num_class; ++k) wmax = fmax(score[static_cast<size_t>(n) * k + i], wmax);
+    double wsum = 0.0f;
+    for (int k = 0; k < num_class; ++k) wsum += exp(score[static_cast<size_t>(n) * k + i] - wmax);
+    const int lab = static_cast<int>(label[i]);
+    for (int k = 0; k < num_class; ++k) {
+      const size_t idx = static_cast<size_t>(n) * k + i;
+      const double p = exp(score[idx] - wmax) / wsum;
+      if (weight == nullptr) {
+        grad[idx] = lab == k ? static_cast<float>(p - 1.0f) : static_cast<float>(p);
+        hess[idx] = static_cast<float>(factor * p * (1.0f - p));
+      } else {
+        grad[idx] = lab == k ? static_cast<float>((p - 1.0f) * weight[i]) : static_cast<float>(p * weight[i]);
+        hess[idx] = static_cast<float>((factor * p * (1.0f - p)) * weight[i]);
+      }
     }
   }
 }
@@ -133,6 +163,13 @@ static Objective* objective_create(const gbl_objective_config* cfg, int64_t num_
       case GBL_OBJ_LAMBDARANK:
         rank_objective_init(o, cfg, label, weight, qb, num_queries);
         break;
+      case GBL_OBJ_MULTICLASS:
+        if (cfg->num_class < 2) fatal("objective: num_class=%d (multiclass needs at least two classes)", cfg->num_class);
+        for (int64_t i = 0; i < num_data; ++i) {  // MulticlassSoftmax::Init, multiclass_objective.hpp:62-66
+          const int l = static_cast<int>(label[i]);
+          if (l < 0 || l >= cfg->num_class) fatal("Label must be in [0, %d), but found %d in label", cfg->num_class, l);
+        }
+        break;
       default:
         fatal("objective: unknown kind %d", cfg->kind);
     }
@@ -168,6 +205,10 @@ static void objective_get_gradients(Objective* o, const double* score, float* gr
       break;
     case GBL_OBJ_LAMBDARANK:
       rank_objective_get_gradients(o, score, grad, hess, s);
+      break;
+    case GBL_OBJ_MULTICLASS:
+      GBL_LAUNCH(multiclass_gradients_kernel, grid, 256, 0, s, score, o->label, o->weight, n, o->cfg.num_class,
+                 static_cast<double>(o->cfg.num_class) / (o->cfg.num_class - 1.0f), grad, hess);
       break;
     default:
       fatal("objective: unknown kind");

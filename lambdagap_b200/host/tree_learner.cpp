@@ -280,7 +280,7 @@ void ObjectiveFunction::Init(const Metadata& metadata, data_size_t num_data, int
   c.sigmoid = config_.sigmoid;
   c.lambdagap_weight = config_.lambdagap_weight;
   c.is_unbalance = config_.is_unbalance ? 1 : 0;
-  c.reserved = 0;
+  c.num_class = 0;
   c.scale_pos_weight = config_.scale_pos_weight;
   c.num_label_gain = static_cast<int>(config_.label_gain.size());
   c.reserved2 = 0;

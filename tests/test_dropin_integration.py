@@ -233,14 +233,19 @@ def test_dropin_rollback_one_iter(gpu, tmp_path):
     np.testing.assert_allclose(s_ours, b.train_scores(), rtol=1e-5, atol=1e-9)
 
 
-def test_dropin_multiclass(gpu, tmp_path):
-    """num_class trees per iteration: GBDT calls TreeLearner::Train once per class with offset gradient pointers."""
+@pytest.mark.parametrize("route", ["device_objective", "device_objective_weighted", "host_objective"])
+def test_dropin_multiclass(gpu, tmp_path, route):
+    """num_class trees per iteration: GBDT calls TreeLearner::Train once per class with offset gradient pointers.  The
+    softmax gradients come from the device objective (class-major blocks, one Train per block from the device copy) or,
+    with GBL_DROPIN_DEVICE_OBJECTIVE=0, from the reference's host objective."""
     rng = np.random.default_rng(5)
     X = rng.normal(size=(60_000, 12)).astype(np.float32)
-    y = (np.argmax(X[:, :3] + 0.3 * rng.normal(size=(len(X), 3)), axis=1)).astype(np.float32)
-    params = "objective=multiclass num_class=3 num_leaves=31 learning_rate=0.1 verbose=-1 num_threads=4"
-    ours, s_ours = _run_dropin(tmp_path, X, y, params + " device_type=cuda", 3)
-    ref, s_ref = _run_reference(X, y, params, 3)
+    y = (np.argmax(X[:, :4] + 0.3 * rng.normal(size=(len(X), 4)), axis=1)).astype(np.float32)
+    w = rng.uniform(0.5, 2.0, size=len(y)).astype(np.float32) if route.endswith("weighted") else None
+    params = "objective=multiclass num_class=4 num_leaves=31 learning_rate=0.1 verbose=-1 num_threads=4"
+    env = {"GBL_DROPIN_DEVICE_OBJECTIVE": "0"} if route == "host_objective" else None
+    ours, s_ours = _run_dropin(tmp_path, X, y, params + " device_type=cuda", 3, weight=w, env=env)
+    ref, s_ref = _run_reference(X, y, params, 3, weight=w)
     _assert_models(ours, ref, 1e-5)
     np.testing.assert_allclose(s_ours, s_ref, rtol=1e-5, atol=1e-9)
 
