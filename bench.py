@@ -550,9 +550,9 @@ def shape_leg(ctx, which, steps, warmup):
     return out
 
 
-def _json_leg(cmd, timeout_s):
+def _json_leg(cmd, timeout_s, env=None):
     try:
-        r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout_s)
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout_s, env=env)
         for line in reversed(r.stdout.strip().split("\n")):
             if line.startswith("{"):
                 return json.loads(line)
@@ -563,12 +563,22 @@ def _json_leg(cmd, timeout_s):
         return {"error": str(ex)[:300]}
 
 
-def dropin_leg(rows, timeout_s=240):
-    """The reference library with the B200 learner compiled in behind its TreeLearner interface (integration/_ref): the
-    reference's own GBDT on the host (gradients, scores), device_type=cuda -> B200TreeLearner.  Own process."""
+def dropin_leg(rows, timeout_s=240, workload="higgs"):
+    """The reference library with the B200 objective and learner compiled in behind its own interfaces (integration/_ref):
+    the reference's GBDT, score array and model on the host, device_type=cuda -> B200Objective + B200TreeLearner.  Own
+    process.  workload "mslr": the MSLR shape with lambdarank (beside it the same library with the reference's host
+    objective, whose pairwise gradients are what the device objective replaces)."""
     if not os.path.exists(os.path.join(ROOT, "integration", "_ref", "lib_lightgbm.so")):
         return {"unavailable": "integration/_ref/lib_lightgbm.so not built (integration/Makefile needs /root/reference)"}
-    return _json_leg([sys.executable, os.path.join(ROOT, "scripts", "dropin_speed.py"), str(rows)], timeout_s)
+    script = os.path.join(ROOT, "scripts", "dropin_speed.py")
+    if workload == "mslr":
+        out = _json_leg([sys.executable, script, "0", "", "mslr"], timeout_s)
+        if isinstance(out, dict) and "value" in out:
+            env = dict(os.environ, GBL_DROPIN_DEVICE_OBJECTIVE="0")
+            host = _json_leg([sys.executable, script, "0", "", "mslr"], timeout_s, env=env)
+            out["with_host_objective"] = host.get("value") if isinstance(host, dict) else None
+        return out
+    return _json_leg([sys.executable, script, str(rows)], timeout_s)
 
 
 def reference_cuda_leg(rows, timeout_s=240):
@@ -822,6 +832,8 @@ def main():
                     shapes[which] = shape_leg(ctx, which, min(args.steps, 8), 3)
                 except Exception as ex:
                     shapes[which] = {"error": str(ex)[:300]}
+            if isinstance(shapes.get("mslr"), dict) and "value" in shapes["mslr"] and not args.quantized:
+                shapes["mslr"]["dropin"] = dropin_leg(0, workload="mslr")
 
     if rank == 0:
         out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
