@@ -167,7 +167,7 @@ __global__ void __launch_bounds__(256) xchg_wave_kernel(LearnerDev d, int is_roo
         v = 0xffffffffu;
         break;
       }
-      __nanosleep(100);
+      __nanosleep(20);
     }
     s_flag = v == 0xffffffffu ? 0 : 1;
   }
@@ -199,11 +199,14 @@ __global__ void __launch_bounds__(256) xchg_wave_kernel(LearnerDev d, int is_roo
     }
   }
   // ---- completion: the last CTA of this rank tells every rank and waits for theirs
-  __threadfence_system();  // every thread: its stores into the peers' pools are visible system-wide before the count
+  // every thread orders its stores into the peers' pools before the CTA's count at GPU scope; the one thread that sees the
+  // last count then fences at system scope before it raises the flag the peers wait for (release is cumulative over the
+  // counts it has observed), instead of 37 000 threads fencing at system scope each
+  __threadfence();
   __syncthreads();
   if (threadIdx.x == 0) {
-    __threadfence_system();
     const unsigned prev = atomicAdd(x.done, 1u);
+    __threadfence_system();
     s_flag = prev == gridDim.x - 1u ? 1 : 0;
   }
   __syncthreads();
@@ -254,8 +257,9 @@ __global__ void __launch_bounds__(32) xchg_max_kernel(LearnerDev d) {
 }
 
 // Default: three launches.  The one-kernel form (GBL_XCHG_FUSED=1) was measured slower on two B200s, Higgs shape,
-// weak scaling: 4.38 ms per tree against 4.21 ms (4.45 ms when every CTA polled the peers' flags itself) -- the
-// launches it saves cost less than the 148 CTAs it parks in front of the barrier.
+// weak scaling: 4.38 ms per tree against 4.21 ms (4.45 ms when every CTA polled the peers' flags itself); with GPU-scope
+// fences per thread and one system-scope fence before the flag, 4.32 against 4.26 ms -- the launches it saves still cost
+// less than the 148 CTAs it parks in front of the barrier.
 bool xchg_fused_enabled() {
   static const bool fused = [] {
     const char* e = std::getenv("GBL_XCHG_FUSED");
