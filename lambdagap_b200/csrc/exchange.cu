@@ -222,6 +222,61 @@ __global__ void __launch_bounds__(256) xchg_wave_kernel(LearnerDev d, int is_roo
   }
 }
 
+// Two-launch form: the barrier kernel in front (all local histograms complete), then the reduction with the SECOND barrier
+// in its tail -- the CTA that finishes last raises this rank's flag and waits for the others.  Nothing is parked in front of
+// a barrier (every other CTA has retired by then); one launch per wave less than the three-launch form.  GBL_XCHG_FUSED=2;
+// measured on two B200s (Higgs shape, weak scaling): 4.31-4.32 ms per tree against 4.25-4.27 ms for three launches --
+// inside a CUDA graph a 32-thread kernel between two others costs less than the fence + count every CTA pays here.
+__global__ void __launch_bounds__(256) xchg_reduce_tail_kernel(LearnerDev d, int is_root) {
+  const TreeState& t = *d.ts;
+  if (!is_root && (t.done || t.last_wave)) return;
+  const PeerX& x = d.px;
+  if (*reinterpret_cast<volatile unsigned*>(x.dead) != 0u) return;
+  const int R = d.p.num_ranks, me = x.rank;
+  const long long slot0 = is_root ? 0 : d.wave[0].hist_slot;
+  const long long C = is_root ? 1 : t.num_cand;
+  const long long units = C * (d.slot_stride >> 1);  // 16-byte units (slot_stride is even)
+  const long long chunk = (units + R - 1) / R;
+  const long long u0 = me * chunk, u1 = min(units, u0 + chunk);
+  const long long base = slot0 * (d.slot_stride >> 1);
+  const long long gsize = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long u = u0 + static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; u < u1; u += gsize) {
+    longlong2 acc = make_longlong2(0, 0);
+    for (int r0 = 0; r0 < R; r0 += 8) {
+      longlong2 v[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {  // up to 8 loads in flight
+        v[k] = make_longlong2(0, 0);
+        if (r0 + k < R) v[k] = reinterpret_cast<const longlong2*>(x.pool[r0 + k])[base + u];
+      }
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        acc.x += v[k].x;
+        acc.y += v[k].y;
+      }
+    }
+    for (int r = 0; r < R; ++r) reinterpret_cast<longlong2*>(x.pool[r])[base + u] = acc;
+  }
+  // completion: GPU-scope fence per thread, the CTA's count, and the last CTA meets the other ranks
+  __shared__ int s_last;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned prev = atomicAdd(x.done, 1u);
+    __threadfence_system();
+    s_last = prev == gridDim.x - 1u ? 1 : 0;
+  }
+  __syncthreads();
+  if (!s_last || threadIdx.x >= 32) return;
+  const unsigned e = *reinterpret_cast<volatile unsigned*>(x.epoch) + 1u;
+  if (threadIdx.x < R) peer_barrier(d, e, threadIdx.x, true);
+  __syncwarp();
+  if (threadIdx.x == 0) {
+    *x.epoch = e;
+    *x.done = 0u;
+  }
+}
+
 // max |gradient|, max |hessian| over ranks in one kernel: every rank deposits its pair with every rank, meets the others
 // at a barrier and takes the maximum of the R deposits (GradientDiscretizer's GlobalSyncUpByMax, also the float scale)
 __global__ void __launch_bounds__(32) xchg_max_kernel(LearnerDev d) {
@@ -260,17 +315,22 @@ __global__ void __launch_bounds__(32) xchg_max_kernel(LearnerDev d) {
 // weak scaling: 4.38 ms per tree against 4.21 ms (4.45 ms when every CTA polled the peers' flags itself); with GPU-scope
 // fences per thread and one system-scope fence before the flag, 4.32 against 4.26 ms -- the launches it saves still cost
 // less than the 148 CTAs it parks in front of the barrier.
-bool xchg_fused_enabled() {
-  static const bool fused = [] {
+static int xchg_mode() {
+  static const int mode = [] {
     const char* e = std::getenv("GBL_XCHG_FUSED");
-    return e != nullptr && e[0] == '1';
+    return e == nullptr ? 0 : std::atoi(e);
   }();
-  return fused;
+  return mode;
 }
+bool xchg_fused_enabled() { return xchg_mode() == 1; }
+int xchg_launches_per_wave() { return xchg_mode() == 1 ? 1 : (xchg_mode() == 2 ? 2 : 3); }
 
 void launch_xchg_wave(const LearnerDev& d, int is_root, cudaStream_t s) {
-  if (xchg_fused_enabled()) {
+  if (xchg_mode() == 1) {
     GBL_LAUNCH(xchg_wave_kernel, kNumSM, 256, 0, s, d, is_root);
+  } else if (xchg_mode() == 2) {
+    GBL_LAUNCH(xchg_barrier_kernel, 1, 32, 0, s, d);
+    GBL_LAUNCH(xchg_reduce_tail_kernel, kNumSM, 256, 0, s, d, is_root);
   } else {
     GBL_LAUNCH(xchg_barrier_kernel, 1, 32, 0, s, d);
     GBL_LAUNCH(xchg_reduce_kernel, kNumSM, 256, 0, s, d, is_root);

@@ -108,7 +108,8 @@ void launch_build_records(uint8_t* rec, int rec_stride, int tile_stride, const u
 void launch_tree_begin(const LearnerDev& d, const int* bag_indices, int bag_count, const int* bag_count_dev, cudaStream_t s);
 // exchange.cu
 void launch_xchg_wave(const LearnerDev& d, int is_root, cudaStream_t s);  // barrier + in-place sum over ranks + barrier
-bool xchg_fused_enabled();  // GBL_XCHG_FUSED=1: the exchange as one kernel instead of three launches
+bool xchg_fused_enabled();
+int xchg_launches_per_wave();  // 3 (default), 2 or 1: GBL_XCHG_FUSED  // GBL_XCHG_FUSED=1: the exchange as one kernel instead of three launches
 void launch_xchg_max(const LearnerDev& d, cudaStream_t s);
 // bagging.cu
 void launch_bag_seed(unsigned* state, int nblk, int seed, cudaStream_t s);

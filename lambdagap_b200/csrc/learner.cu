@@ -896,7 +896,7 @@ static void train_async(Learner* L, const float* grad_dev, const float* hess_dev
 // waves): prologue (tree_begin, [bagged index copy], maxabs, scales, histogram, root_init, scan, select) + 6 per
 // wave + the replay
 static long long kernels_of_tree(const Learner* L, const TreeState& t) {
-  const long long per_xchg = xchg_fused_enabled() ? 1 : 3;  // barrier / reduce / barrier, or the one-kernel form
+  const long long per_xchg = xchg_launches_per_wave();  // barrier / reduce / barrier, or the two- / one-kernel forms
   const long long xchg = L->peer ? 1 + per_xchg * (1 + t.waves) : 0;  // max exchange, root sum, one exchange per wave
   return (L->bag_indices != nullptr ? 8 : 7) + 6LL * t.waves + 1 + xchg +
          ((L->cfg.use_quantized_grad && L->cfg.quant_train_renew_leaf) ? 3 : 0);
